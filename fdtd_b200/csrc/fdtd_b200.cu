@@ -1,0 +1,891 @@
+// C ABI of fdtd_b200 (include/fdtd_b200.h): host-side state and kernel launches.
+// Reference behaviour being replaced: cem-solver/src/fdtd/cpu/mod.rs (instance, state, update pass,
+// field views), cem-solver/src/fdtd/wgpu/mod.rs (fp32 data layout), cem-solver/src/fdtd/util.rs
+// (coefficients), cem-solver/src/fdtd/cpu/project.rs + wgpu/project.wgsl (projection).
+#include "../../include/fdtd_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace fdtd_b200;
+
+namespace {
+
+thread_local std::string g_error;
+
+struct Tune {
+    int bx = 0, by = 0, zc = 0;  // 0 = choose automatically
+};
+
+}  // namespace
+
+struct fdtd_b200_solver {
+    fdtd_b200_config cfg{};
+    uint64_t nx = 0, ny = 0, nz = 0;   // global
+    uint64_t z_begin = 0, z_end = 0;   // slab
+    uint64_t nzl = 0;                  // owned planes
+    uint64_t plane = 0;                // nx*ny
+    uint64_t n_local = 0;              // plane*nzl
+    int device = 0;
+    uint32_t flags = 0;
+    bool vec4 = false;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+
+    float* alloc[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // ghost + planes + ghost
+    float* f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};      // plane 0
+    void* mat = nullptr;
+    int idx_bytes = 1;
+    float4* table = nullptr;
+    uint32_t n_table = 0;
+
+    // forcing table: rows consumed one per step
+    long long* d_src_cells = nullptr;  // sorted local indices
+    float* d_src_vals = nullptr;       // [rows][n_src][6]
+    uint32_t n_src = 0;
+    uint64_t src_rows = 0, src_row = 0;
+    size_t src_cells_cap = 0, src_vals_cap = 0;
+
+    // probes
+    long long* d_probe_cells = nullptr;
+    int* d_probe_slot = nullptr;
+    float* d_probe_ring = nullptr;  // [ring_steps][n_probes_total][6]
+    uint32_t n_probes_total = 0, n_probes_local = 0;
+    uint32_t ring_steps = 0;
+    uint64_t probe_first_tick = 0;  // tick at registration
+
+    // scratch for read/write_field
+    float* d_stage = nullptr;
+    size_t stage_floats = 0;
+
+    uint64_t tick = 0;
+    double time = 0.0;
+    uint64_t launches = 0;
+    Tune tune;
+    std::string err;
+};
+
+namespace {
+
+int fail(fdtd_b200_handle h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    g_error = msg;
+    return code;
+}
+
+#define CU_TRY(h, expr)                                                                                    \
+    do {                                                                                                   \
+        cudaError_t e__ = (expr);                                                                          \
+        if (e__ != cudaSuccess) {                                                                          \
+            (void)cudaGetLastError();                                                                      \
+            return fail((h), e__ == cudaErrorMemoryAllocation ? FDTD_B200_ENOMEM : FDTD_B200_ECUDA,        \
+                        std::string(#expr) + ": " + cudaGetErrorString(e__));                              \
+        }                                                                                                  \
+    } while (0)
+
+struct MatKey {
+    uint64_t w[4];
+    bool operator==(const MatKey& o) const { return std::memcmp(w, o.w, sizeof w) == 0; }
+};
+struct MatKeyHash {
+    size_t operator()(const MatKey& k) const {
+        uint64_t h = 0x9E3779B97F4A7C15ull;
+        for (uint64_t v : k.w) { h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2); }
+        return static_cast<size_t>(h);
+    }
+};
+MatKey key_of(const fdtd_b200_material& m) {
+    MatKey k;
+    static_assert(sizeof(fdtd_b200_material) == sizeof(k.w), "material is four doubles");
+    std::memcpy(k.w, &m, sizeof k.w);
+    return k;
+}
+
+bool c_or_d(double perm, double sigma, double dt, double* a, double* b) {
+    // fdtd/util.rs:104-116
+    const double x = 0.5 * sigma * dt / perm;
+    *a = (1.0 - x) / (1.0 + x);
+    *b = dt / (perm * (1.0 + x));
+    return !(std::isnan(*a) || std::isnan(*b));
+}
+
+Tune parse_tune() {
+    Tune t;
+    if (const char* s = std::getenv("FDTD_B200_TUNE")) {
+        int a = 0, b = 0, c = 0;
+        if (std::sscanf(s, "%d,%d,%d", &a, &b, &c) >= 1) { t.bx = a; t.by = b; t.zc = c; }
+    }
+    return t;
+}
+
+int set_device(fdtd_b200_handle h) {
+    CU_TRY(h, cudaSetDevice(h->device));
+    return FDTD_B200_OK;
+}
+
+LatticeView lattice_view(fdtd_b200_handle h) {
+    LatticeView L{};
+    L.ex = h->f[0]; L.ey = h->f[1]; L.ez = h->f[2];
+    L.hx = h->f[3]; L.hy = h->f[4]; L.hz = h->f[5];
+    L.mat = h->mat;
+    L.table = h->table;
+    L.n_table = static_cast<int>(h->n_table);
+    L.table_in_smem = h->n_table <= 4096 ? 1 : 0;
+    L.nx = static_cast<int>(h->nx); L.ny = static_cast<int>(h->ny); L.nz = static_cast<int>(h->nzl);
+    L.lo_open = h->z_begin > 0 ? 1 : 0;
+    L.hi_open = h->z_end < h->nz ? 1 : 0;
+    for (int a = 0; a < 3; ++a) {
+        L.dx[a] = static_cast<float>(h->cfg.dx[a]);  // resolution cast to f32 as wgpu/mod.rs:606-612
+        L.inv_dx[a] = 1.0f / L.dx[a];
+    }
+    return L;
+}
+
+ForcingView forcing_view(fdtd_b200_handle h) {
+    ForcingView F{};
+    if (h->n_src && h->src_row < h->src_rows) {
+        F.n = static_cast<int>(h->n_src);
+        F.cells = h->d_src_cells;
+        F.vals = h->d_src_vals + h->src_row * static_cast<uint64_t>(h->n_src) * 6;
+    }
+    return F;
+}
+
+ProbeView probe_view(fdtd_b200_handle h) {
+    ProbeView P{};
+    if (h->n_probes_local) {
+        P.n = static_cast<int>(h->n_probes_local);
+        P.cells = h->d_probe_cells;
+        P.slot = h->d_probe_slot;
+        P.row = h->d_probe_ring + (h->tick % h->ring_steps) * static_cast<uint64_t>(h->n_probes_total) * 6;
+    }
+    return P;
+}
+
+// ---- kernel dispatch ---------------------------------------------------------------------------
+
+using HKernel = void (*)(LatticeView, ForcingView, int, int, int);
+using EKernel = void (*)(LatticeView, ForcingView, ProbeView, int, int, int);
+
+struct Shape { int bx, by; };
+constexpr Shape kShapes[] = {{32, 4}, {32, 8}, {64, 2}, {64, 4}, {128, 1}, {128, 2}, {128, 4}};
+constexpr int kNumShapes = sizeof(kShapes) / sizeof(kShapes[0]);
+
+template <bool EXACT, typename IdxT>
+HKernel h_kernel(int shape) {
+    switch (shape) {
+        case 0: return k_update_h_vec4<EXACT, IdxT, 32, 4>;
+        case 1: return k_update_h_vec4<EXACT, IdxT, 32, 8>;
+        case 2: return k_update_h_vec4<EXACT, IdxT, 64, 2>;
+        case 3: return k_update_h_vec4<EXACT, IdxT, 64, 4>;
+        case 4: return k_update_h_vec4<EXACT, IdxT, 128, 1>;
+        case 5: return k_update_h_vec4<EXACT, IdxT, 128, 2>;
+        default: return k_update_h_vec4<EXACT, IdxT, 128, 4>;
+    }
+}
+template <bool EXACT, typename IdxT>
+EKernel e_kernel(int shape) {
+    switch (shape) {
+        case 0: return k_update_e_vec4<EXACT, IdxT, 32, 4>;
+        case 1: return k_update_e_vec4<EXACT, IdxT, 32, 8>;
+        case 2: return k_update_e_vec4<EXACT, IdxT, 64, 2>;
+        case 3: return k_update_e_vec4<EXACT, IdxT, 64, 4>;
+        case 4: return k_update_e_vec4<EXACT, IdxT, 128, 1>;
+        case 5: return k_update_e_vec4<EXACT, IdxT, 128, 2>;
+        default: return k_update_e_vec4<EXACT, IdxT, 128, 4>;
+    }
+}
+
+int pick_shape(fdtd_b200_handle h) {
+    const int quads = static_cast<int>(h->nx / 4);
+    int bx = h->tune.bx, by = h->tune.by;
+    if (bx == 0) bx = quads >= 128 ? 128 : (quads > 32 ? 64 : 32);
+    if (by == 0) by = 256 / bx;
+    for (int s = 0; s < kNumShapes; ++s)
+        if (kShapes[s].bx == bx && kShapes[s].by == by) return s;
+    return bx >= 128 ? 5 : (bx == 64 ? 3 : 1);
+}
+
+int pick_zc(fdtd_b200_handle h, int planes) {
+    if (h->tune.zc > 0) return h->tune.zc;
+    // enough CTAs for several waves over 148 SMs, but long enough marches that the extra
+    // z∓1 prologue plane (2 of 9 streams) stays a small fraction of the traffic
+    const Shape sh = kShapes[pick_shape(h)];
+    const long long row_blocks = ((static_cast<long long>(h->nx) / 4 + sh.bx - 1) / sh.bx) * ((static_cast<long long>(h->ny) + sh.by - 1) / sh.by);
+    int zc = 32;
+    while (zc > 4 && row_blocks * ((planes + zc - 1) / zc) < 148LL * 16) zc >>= 1;
+    return zc;
+}
+
+template <bool EXACT, typename IdxT>
+int launch_h_t(fdtd_b200_handle h, int z_lo, int z_hi) {
+    const LatticeView L = lattice_view(h);
+    const ForcingView F = forcing_view(h);
+    if (h->vec4) {
+        const int s = pick_shape(h);
+        const Shape sh = kShapes[s];
+        const int zc = pick_zc(h, z_hi - z_lo);
+        dim3 block(sh.bx, sh.by, 1);
+        dim3 grid((L.nx / 4 + sh.bx - 1) / sh.bx, (L.ny + sh.by - 1) / sh.by, (z_hi - z_lo + zc - 1) / zc);
+        const size_t smem = L.table_in_smem ? sizeof(float2) * h->n_table : 0;
+        h_kernel<EXACT, IdxT>(s)<<<grid, block, smem, h->stream>>>(L, F, z_lo, z_hi, zc);
+    } else {
+        dim3 block(64, 4, 1);
+        dim3 grid((L.nx + 63) / 64, (L.ny + 3) / 4, std::min(z_hi - z_lo, 65535));
+        k_update_h_generic<EXACT, IdxT><<<grid, block, 0, h->stream>>>(L, F, z_lo, z_hi);
+    }
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+template <bool EXACT, typename IdxT>
+int launch_e_t(fdtd_b200_handle h, int z_lo, int z_hi) {
+    const LatticeView L = lattice_view(h);
+    const ForcingView F = forcing_view(h);
+    const ProbeView P = probe_view(h);
+    if (h->vec4) {
+        const int s = pick_shape(h);
+        const Shape sh = kShapes[s];
+        const int zc = pick_zc(h, z_hi - z_lo);
+        dim3 block(sh.bx, sh.by, 1);
+        dim3 grid((L.nx / 4 + sh.bx - 1) / sh.bx, (L.ny + sh.by - 1) / sh.by, (z_hi - z_lo + zc - 1) / zc);
+        const size_t smem = L.table_in_smem ? sizeof(float2) * h->n_table : 0;
+        e_kernel<EXACT, IdxT>(s)<<<grid, block, smem, h->stream>>>(L, F, P, z_lo, z_hi, zc);
+    } else {
+        dim3 block(64, 4, 1);
+        dim3 grid((L.nx + 63) / 64, (L.ny + 3) / 4, std::min(z_hi - z_lo, 65535));
+        k_update_e_generic<EXACT, IdxT><<<grid, block, 0, h->stream>>>(L, F, P, z_lo, z_hi);
+    }
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+int launch_h(fdtd_b200_handle h, int z_lo, int z_hi) {
+    if (z_lo >= z_hi) return FDTD_B200_OK;
+    const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
+    if (h->idx_bytes == 1) return exact ? launch_h_t<true, uint8_t>(h, z_lo, z_hi) : launch_h_t<false, uint8_t>(h, z_lo, z_hi);
+    return exact ? launch_h_t<true, uint16_t>(h, z_lo, z_hi) : launch_h_t<false, uint16_t>(h, z_lo, z_hi);
+}
+int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
+    if (z_lo >= z_hi) return FDTD_B200_OK;
+    const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
+    if (h->idx_bytes == 1) return exact ? launch_e_t<true, uint8_t>(h, z_lo, z_hi) : launch_e_t<false, uint8_t>(h, z_lo, z_hi);
+    return exact ? launch_e_t<true, uint16_t>(h, z_lo, z_hi) : launch_e_t<false, uint16_t>(h, z_lo, z_hi);
+}
+
+void end_step(fdtd_b200_handle h) {
+    h->tick += 1;
+    h->time += h->cfg.dt;  // accumulated (cpu/mod.rs:513), never tick*dt
+    if (h->n_src) {
+        h->src_row += 1;
+        if (h->src_row >= h->src_rows) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; }  // forcing is per step (cpu/mod.rs:370-377)
+    }
+}
+
+int ensure_stage(fdtd_b200_handle h, size_t floats) {
+    if (h->stage_floats >= floats) return FDTD_B200_OK;
+    if (h->d_stage) { cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_floats = 0; }
+    CU_TRY(h, cudaMalloc(&h->d_stage, floats * sizeof(float)));
+    h->stage_floats = floats;
+    return FDTD_B200_OK;
+}
+
+bool validate_cfg(const fdtd_b200_config* cfg, std::string* why) {
+    if (!cfg) { *why = "config is NULL"; return false; }
+    if (cfg->nx == 0 || cfg->ny == 0 || cfg->nz == 0) { *why = "lattice dimensions must be >= 1 (fdtd/mod.rs:25-29 clamps to 1)"; return false; }
+    if (cfg->nx > 0x7fffffffull || cfg->ny > 0x7fffffffull || cfg->nz > 0x7fffffffull) { *why = "lattice dimension exceeds 2^31-1"; return false; }
+    for (int a = 0; a < 3; ++a)
+        if (!(cfg->dx[a] > 0.0) || !std::isfinite(cfg->dx[a])) { *why = "dx must be finite and > 0"; return false; }
+    if (!std::isfinite(cfg->dt)) { *why = "dt must be finite"; return false; }
+    const uint64_t zb = cfg->z_begin, ze = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
+    if (zb >= ze || ze > cfg->nz) { *why = "z-slab [z_begin, z_end) is empty or outside the lattice"; return false; }
+    return true;
+}
+
+int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
+                  const uint32_t* material_ids, fdtd_b200_handle* out) {
+    std::string why;
+    if (!out) return fail(nullptr, FDTD_B200_EINVAL, "out handle pointer is NULL");
+    *out = nullptr;
+    if (!validate_cfg(cfg, &why)) return fail(nullptr, FDTD_B200_EINVAL, why);
+    if (!table || n_table == 0 || n_table > 65536) return fail(nullptr, FDTD_B200_EINVAL, "coefficient table must hold 1..65536 entries");
+
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+        (void)cudaGetLastError();
+        return fail(nullptr, FDTD_B200_ECUDA, "no CUDA device available: fdtd_b200 has no CPU fallback");
+    }
+    if (cfg->device < 0 || cfg->device >= n_dev) return fail(nullptr, FDTD_B200_EINVAL, "device ordinal out of range");
+
+    auto* h = new fdtd_b200_solver();
+    h->cfg = *cfg;
+    h->nx = cfg->nx; h->ny = cfg->ny; h->nz = cfg->nz;
+    h->z_begin = cfg->z_begin;
+    h->z_end = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
+    h->nzl = h->z_end - h->z_begin;
+    h->plane = h->nx * h->ny;
+    h->n_local = h->plane * h->nzl;
+    h->device = cfg->device;
+    h->flags = cfg->flags;
+    h->vec4 = (h->nx % 4 == 0) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS);
+    h->idx_bytes = n_table <= 256 ? 1 : 2;
+    h->n_table = n_table;
+    h->ring_steps = cfg->probe_ring_steps ? cfg->probe_ring_steps : 4096;
+    h->tune = parse_tune();
+
+    auto bail = [&](int code) { std::string m = h->err; fdtd_b200_destroy(h); g_error = m; return code; };
+#define CU_NEW(expr)                                                                                            \
+    do {                                                                                                        \
+        cudaError_t e__ = (expr);                                                                               \
+        if (e__ != cudaSuccess) {                                                                               \
+            (void)cudaGetLastError();                                                                           \
+            h->err = std::string(#expr) + ": " + cudaGetErrorString(e__);                                       \
+            return bail(e__ == cudaErrorMemoryAllocation ? FDTD_B200_ENOMEM : FDTD_B200_ECUDA);                 \
+        }                                                                                                       \
+    } while (0)
+
+    CU_NEW(cudaSetDevice(h->device));
+    CU_NEW(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
+
+    // fields: [ghost plane][nzl planes][ghost plane] per scalar component, zero-initialised (cpu/mod.rs:314-316)
+    const size_t comp_floats = static_cast<size_t>(h->plane) * (h->nzl + 2);
+    for (int c = 0; c < 6; ++c) {
+        CU_NEW(cudaMalloc(&h->alloc[c], comp_floats * sizeof(float)));
+        CU_NEW(cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
+        h->f[c] = h->alloc[c] + h->plane;
+    }
+    // material index (+8 bytes slack so the last quad's vector load never leaves the allocation)
+    CU_NEW(cudaMalloc(&h->mat, h->n_local * h->idx_bytes + 16));
+    if (!material_ids) {
+        CU_NEW(cudaMemsetAsync(h->mat, 0, h->n_local * h->idx_bytes + 16, h->stream));
+    } else {
+        // stream the u32 ids through a bounded staging buffer and narrow them on the device
+        const size_t chunk = std::min<size_t>(h->n_local, size_t(1) << 24);
+        uint32_t* d_ids = nullptr;
+        CU_NEW(cudaMalloc(&d_ids, chunk * sizeof(uint32_t)));
+        for (size_t off = 0; off < h->n_local; off += chunk) {
+            const size_t n = std::min(chunk, static_cast<size_t>(h->n_local) - off);
+            for (size_t i = 0; i < n; ++i) {
+                if (material_ids[off + i] >= n_table) {
+                    cudaFree(d_ids);
+                    h->err = "material id out of range of the palette/table";
+                    return bail(FDTD_B200_EINVAL);
+                }
+            }
+            cudaError_t e = cudaMemcpyAsync(d_ids, material_ids + off, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream);
+            if (e == cudaSuccess) {
+                const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 148 * 8));
+                if (h->idx_bytes == 1) k_narrow_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint8_t*>(h->mat) + off, n);
+                else k_narrow_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint16_t*>(h->mat) + off, n);
+                h->launches += 1;
+                e = cudaStreamSynchronize(h->stream);
+            }
+            if (e != cudaSuccess) { cudaFree(d_ids); h->err = std::string("material upload: ") + cudaGetErrorString(e); return bail(FDTD_B200_ECUDA); }
+        }
+        cudaFree(d_ids);
+    }
+    CU_NEW(cudaMalloc(&h->table, sizeof(float4) * n_table));
+    static_assert(sizeof(fdtd_b200_coefficients_f32) == sizeof(float4), "table entry is four floats");
+    CU_NEW(cudaMemcpyAsync(h->table, table, sizeof(float4) * n_table, cudaMemcpyHostToDevice, h->stream));
+    CU_NEW(cudaStreamSynchronize(h->stream));
+#undef CU_NEW
+    *out = h;
+    return FDTD_B200_OK;
+}
+
+// global box → local BoxView; EINVAL when empty or outside slab
+int make_box(fdtd_b200_handle h, const uint64_t lo[3], const uint64_t hi[3], BoxView* B, size_t* n_cells) {
+    if (!lo || !hi) return fail(h, FDTD_B200_EINVAL, "box bounds are NULL");
+    uint64_t l[3], u[3];
+    const uint64_t dims[3] = {h->nx, h->ny, h->nz};
+    for (int a = 0; a < 3; ++a) {
+        l[a] = std::min(lo[a], dims[a]);
+        u[a] = std::min(std::max(hi[a], lo[a]), dims[a]);  // util.rs:157-160: end = max(start, end)
+        if (u[a] < l[a]) u[a] = l[a];
+    }
+    *n_cells = static_cast<size_t>((u[0] - l[0]) * (u[1] - l[1]) * (u[2] - l[2]));
+    if (*n_cells == 0) { *B = BoxView{}; return FDTD_B200_OK; }
+    if (l[2] < h->z_begin || u[2] > h->z_end) return fail(h, FDTD_B200_EINVAL, "box leaves this handle's z-slab");
+    B->x0 = static_cast<int>(l[0]); B->y0 = static_cast<int>(l[1]); B->z0 = static_cast<int>(l[2] - h->z_begin);
+    B->bx = static_cast<int>(u[0] - l[0]); B->by = static_cast<int>(u[1] - l[1]); B->bz = static_cast<int>(u[2] - l[2]);
+    B->nx = static_cast<int>(h->nx); B->ny = static_cast<int>(h->ny);
+    return FDTD_B200_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+extern "C" {
+
+int fdtd_b200_abi_version(void) { return FDTD_B200_ABI_VERSION; }
+
+int fdtd_b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* fdtd_b200_global_error(void) { return g_error.c_str(); }
+
+int fdtd_b200_update_coefficients_new(double dt, const fdtd_b200_physical_constants* pc, const fdtd_b200_material* m,
+                                      fdtd_b200_update_coefficients* out) {
+    if (!pc || !m || !out) return fail(nullptr, FDTD_B200_EINVAL, "NULL argument");
+    const bool ok1 = c_or_d(m->relative_permittivity * pc->vacuum_permittivity, m->eletrical_conductivity, dt, &out->c_a, &out->c_b);
+    const bool ok2 = c_or_d(m->relative_permeability * pc->vacuum_permeability, m->magnetic_conductivity, dt, &out->d_a, &out->d_b);
+    if (!ok1 || !ok2) return fail(nullptr, FDTD_B200_EINVAL, "update coefficient is NaN (fdtd/util.rs:112-113 asserts)");
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_index_materials(const fdtd_b200_material* materials, uint64_t n_cells, uint32_t* ids_out,
+                              fdtd_b200_material* palette_out, uint32_t palette_cap, uint32_t* n_palette_out) {
+    if (!materials || !ids_out || !n_palette_out) return fail(nullptr, FDTD_B200_EINVAL, "NULL argument");
+    std::unordered_map<MatKey, uint32_t, MatKeyHash> seen;
+    uint32_t n = 0;
+    for (uint64_t i = 0; i < n_cells; ++i) {
+        const MatKey k = key_of(materials[i]);
+        auto it = seen.find(k);
+        if (it == seen.end()) {
+            it = seen.emplace(k, n).first;
+            if (n < palette_cap && palette_out) palette_out[n] = materials[i];
+            ++n;
+        }
+        ids_out[i] = it->second;
+    }
+    *n_palette_out = n;
+    if (n > palette_cap) return fail(nullptr, FDTD_B200_EINVAL, "more distinct materials than palette_cap");
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_canonicalize_material_index(const uint32_t* ids_in, uint64_t n_cells, const fdtd_b200_material* palette_in,
+                                          uint32_t n_palette_in, uint32_t* ids_out, fdtd_b200_material* palette_out,
+                                          uint32_t palette_cap, uint32_t* n_palette_out) {
+    if (!ids_in || !palette_in || !ids_out || !n_palette_out) return fail(nullptr, FDTD_B200_EINVAL, "NULL argument");
+    // merge labels that denote bit-identical materials, then renumber by first occurrence
+    std::unordered_map<MatKey, uint32_t, MatKeyHash> canon_of_key;
+    std::vector<uint32_t> merged(n_palette_in);
+    for (uint32_t p = 0; p < n_palette_in; ++p) merged[p] = canon_of_key.emplace(key_of(palette_in[p]), p).first->second;
+    std::vector<uint32_t> new_id(n_palette_in, UINT32_MAX);
+    uint32_t n = 0;
+    for (uint64_t i = 0; i < n_cells; ++i) {
+        const uint32_t lab = ids_in[i];
+        if (lab >= n_palette_in) return fail(nullptr, FDTD_B200_EINVAL, "material id out of range of the palette");
+        const uint32_t rep = merged[lab];
+        if (new_id[rep] == UINT32_MAX) {
+            new_id[rep] = n;
+            if (n < palette_cap && palette_out) palette_out[n] = palette_in[rep];
+            ++n;
+        }
+        ids_out[i] = new_id[rep];
+    }
+    *n_palette_out = n;
+    if (n > palette_cap) return fail(nullptr, FDTD_B200_EINVAL, "more distinct materials than palette_cap");
+    return FDTD_B200_OK;
+}
+
+size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_bytes) {
+    std::string why;
+    if (!validate_cfg(cfg, &why) || (index_bytes != 1 && index_bytes != 2)) return 0;
+    const uint64_t ze = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
+    const uint64_t nzl = ze - cfg->z_begin;
+    const uint64_t plane = cfg->nx * cfg->ny;
+    // 6 fp32 components with two ghost planes each + the material index (cf. 136 B/cell cpu/mod.rs:217-221,
+    // 80 B/cell wgpu/mod.rs:129-133)
+    return static_cast<size_t>(6 * sizeof(float) * plane * (nzl + 2) + plane * nzl * index_bytes + 16);
+}
+
+int fdtd_b200_create_from_table(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
+                                const uint32_t* material_ids, fdtd_b200_handle* out) {
+    return create_common(cfg, table, n_table, material_ids, out);
+}
+
+int fdtd_b200_create(const fdtd_b200_config* cfg, const fdtd_b200_physical_constants* constants,
+                     const fdtd_b200_material* palette, uint32_t n_palette, const uint32_t* material_ids,
+                     fdtd_b200_handle* out) {
+    if (out) *out = nullptr;
+    if (!cfg || !constants || !palette || n_palette == 0 || n_palette > 65536)
+        return fail(nullptr, FDTD_B200_EINVAL, "palette must hold 1..65536 materials");
+    std::vector<fdtd_b200_coefficients_f32> table(n_palette);
+    for (uint32_t k = 0; k < n_palette; ++k) {
+        fdtd_b200_update_coefficients u{};
+        const int rc = fdtd_b200_update_coefficients_new(cfg->dt, constants, &palette[k], &u);
+        if (rc) return rc;
+        // cast once f64 → f32 (wgpu/mod.rs:670-678)
+        table[k] = {static_cast<float>(u.c_a), static_cast<float>(u.c_b), static_cast<float>(u.d_a), static_cast<float>(u.d_b)};
+    }
+    return create_common(cfg, table.data(), n_palette, material_ids, out);
+}
+
+void fdtd_b200_destroy(fdtd_b200_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+    for (int c = 0; c < 6; ++c) if (h->alloc[c]) cudaFree(h->alloc[c]);
+    if (h->mat) cudaFree(h->mat);
+    if (h->table) cudaFree(h->table);
+    if (h->d_src_cells) cudaFree(h->d_src_cells);
+    if (h->d_src_vals) cudaFree(h->d_src_vals);
+    if (h->d_probe_cells) cudaFree(h->d_probe_cells);
+    if (h->d_probe_slot) cudaFree(h->d_probe_slot);
+    if (h->d_probe_ring) cudaFree(h->d_probe_ring);
+    if (h->d_stage) cudaFree(h->d_stage);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    (void)cudaGetLastError();
+    delete h;
+}
+
+const char* fdtd_b200_last_error(fdtd_b200_handle h) { return h ? h->err.c_str() : g_error.c_str(); }
+
+int fdtd_b200_reset(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    const size_t comp_floats = static_cast<size_t>(h->plane) * (h->nzl + 2);
+    for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
+    if (h->d_probe_ring)
+        CU_TRY(h, cudaMemsetAsync(h->d_probe_ring, 0, sizeof(float) * 6 * h->n_probes_total * static_cast<size_t>(h->ring_steps), h->stream));
+    h->n_src = 0; h->src_rows = 0; h->src_row = 0;
+    h->tick = 0;
+    h->time = 0.0;
+    h->probe_first_tick = 0;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_set_stream(fdtd_b200_handle h, void* cuda_stream) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_sync(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return FDTD_B200_OK;
+}
+
+uint64_t fdtd_b200_tick(fdtd_b200_handle h) { return h ? h->tick : 0; }
+double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
+int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }
+int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
+uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h) { return h ? h->launches : 0; }
+
+int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out) {
+    if (!h || !ids_out) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    if (int rc = set_device(h)) return rc;
+    const size_t chunk = std::min<size_t>(h->n_local, size_t(1) << 24);
+    uint32_t* d = nullptr;
+    CU_TRY(h, cudaMalloc(&d, chunk * sizeof(uint32_t)));
+    for (size_t off = 0; off < h->n_local; off += chunk) {
+        const size_t n = std::min(chunk, static_cast<size_t>(h->n_local) - off);
+        const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 148 * 8));
+        if (h->idx_bytes == 1) k_widen_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint8_t*>(h->mat) + off, d, n);
+        else k_widen_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint16_t*>(h->mat) + off, d, n);
+        h->launches += 1;
+        cudaError_t e = cudaMemcpyAsync(ids_out + off, d, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { cudaFree(d); return fail(h, FDTD_B200_ECUDA, std::string("read_material_ids: ") + cudaGetErrorString(e)); }
+    }
+    cudaFree(d);
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_read_coefficient_table(fdtd_b200_handle h, fdtd_b200_coefficients_f32* out, uint32_t cap, uint32_t* n_out) {
+    if (!h || !n_out) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    *n_out = h->n_table;
+    if (!out || cap == 0) return FDTD_B200_OK;
+    if (int rc = set_device(h)) return rc;
+    const uint32_t n = std::min(cap, h->n_table);
+    CU_TRY(h, cudaMemcpyAsync(out, h->table, sizeof(float4) * n, cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return FDTD_B200_OK;
+}
+
+// ---- forcing ---------------------------------------------------------------------------------------
+
+int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_t* cells, uint64_t n_steps, const float* values) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (n_src == 0 || n_steps == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; return FDTD_B200_OK; }
+    if (!cells || !values) return fail(h, FDTD_B200_EINVAL, "NULL cells/values");
+    const uint64_t n_global = h->plane * h->nz;
+    for (uint32_t k = 0; k < n_src; ++k)
+        if (cells[k] >= n_global) return fail(h, FDTD_B200_EINVAL, "set_forcing called with invalid point (cell index outside the lattice)");
+    if (int rc = set_device(h)) return rc;
+
+    // keep the slab's cells; for duplicates the later column wins (cpu/mod.rs:399-408); sort by local index
+    const uint64_t base = h->z_begin * h->plane;
+    std::unordered_map<long long, uint32_t> last;
+    for (uint32_t k = 0; k < n_src; ++k) {
+        if (cells[k] < base || cells[k] >= base + h->n_local) continue;
+        last[static_cast<long long>(cells[k] - base)] = k;
+    }
+    std::vector<std::pair<long long, uint32_t>> kept(last.begin(), last.end());
+    std::sort(kept.begin(), kept.end());
+    const uint32_t m = static_cast<uint32_t>(kept.size());
+    if (m == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; return FDTD_B200_OK; }
+
+    std::vector<long long> lc(m);
+    std::vector<float> vals(static_cast<size_t>(n_steps) * m * 6);
+    for (uint32_t q = 0; q < m; ++q) lc[q] = kept[q].first;
+    for (uint64_t s = 0; s < n_steps; ++s)
+        for (uint32_t q = 0; q < m; ++q)
+            std::memcpy(&vals[(s * m + q) * 6], values + (s * n_src + kept[q].second) * 6, 6 * sizeof(float));
+
+    if (h->src_cells_cap < m) {
+        if (h->d_src_cells) cudaFree(h->d_src_cells);
+        h->d_src_cells = nullptr; h->src_cells_cap = 0;
+        CU_TRY(h, cudaMalloc(&h->d_src_cells, sizeof(long long) * m));
+        h->src_cells_cap = m;
+    }
+    if (h->src_vals_cap < vals.size()) {
+        if (h->d_src_vals) cudaFree(h->d_src_vals);
+        h->d_src_vals = nullptr; h->src_vals_cap = 0;
+        CU_TRY(h, cudaMalloc(&h->d_src_vals, sizeof(float) * vals.size()));
+        h->src_vals_cap = vals.size();
+    }
+    // previously enqueued steps may still be reading the old table
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    CU_TRY(h, cudaMemcpy(h->d_src_cells, lc.data(), sizeof(long long) * m, cudaMemcpyHostToDevice));
+    CU_TRY(h, cudaMemcpy(h->d_src_vals, vals.data(), sizeof(float) * vals.size(), cudaMemcpyHostToDevice));
+    h->n_src = m;
+    h->src_rows = n_steps;
+    h->src_row = 0;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_set_sources(fdtd_b200_handle h, uint32_t n, const fdtd_b200_source* sources) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (n == 0) return fdtd_b200_set_source_table(h, 0, nullptr, 0, nullptr);
+    if (!sources) return fail(h, FDTD_B200_EINVAL, "NULL sources");
+    std::vector<uint64_t> cells(n);
+    std::vector<float> vals(static_cast<size_t>(n) * 6);
+    for (uint32_t k = 0; k < n; ++k) {
+        cells[k] = sources[k].cell;
+        for (int c = 0; c < 3; ++c) { vals[6 * k + c] = sources[k].j[c]; vals[6 * k + 3 + c] = sources[k].m[c]; }
+    }
+    return fdtd_b200_set_source_table(h, n, cells.data(), 1, vals.data());
+}
+
+// ---- stepping --------------------------------------------------------------------------------------
+
+int fdtd_b200_update_h(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (z_hi > h->nzl || z_lo > z_hi) return fail(h, FDTD_B200_EINVAL, "plane range outside the slab");
+    if (int rc = set_device(h)) return rc;
+    return launch_h(h, static_cast<int>(z_lo), static_cast<int>(z_hi));
+}
+
+int fdtd_b200_update_e(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (z_hi > h->nzl || z_lo > z_hi) return fail(h, FDTD_B200_EINVAL, "plane range outside the slab");
+    if (int rc = set_device(h)) return rc;
+    return launch_e(h, static_cast<int>(z_lo), static_cast<int>(z_hi));
+}
+
+int fdtd_b200_end_step(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    end_step(h);
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    const int nzl = static_cast<int>(h->nzl);
+    for (uint64_t s = 0; s < n_steps; ++s) {
+        if (int rc = launch_h(h, 0, nzl)) return rc;
+        if (int rc = launch_e(h, 0, nzl)) return rc;
+        end_step(h);
+    }
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint64_t* n_floats) {
+    if (!h || !device_ptr) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    const size_t top = static_cast<size_t>(h->plane) * (h->nzl - 1);
+    const size_t above = static_cast<size_t>(h->plane) * h->nzl;
+    float* p = nullptr;
+    switch (which) {
+        case FDTD_B200_HALO_SEND_EX_TOP: p = h->f[0] + top; break;
+        case FDTD_B200_HALO_SEND_EY_TOP: p = h->f[1] + top; break;
+        case FDTD_B200_HALO_RECV_EX_LOW: p = h->alloc[0]; break;
+        case FDTD_B200_HALO_RECV_EY_LOW: p = h->alloc[1]; break;
+        case FDTD_B200_HALO_SEND_HX_BOTTOM: p = h->f[3]; break;
+        case FDTD_B200_HALO_SEND_HY_BOTTOM: p = h->f[4]; break;
+        case FDTD_B200_HALO_RECV_HX_HIGH: p = h->f[3] + above; break;
+        case FDTD_B200_HALO_RECV_HY_HIGH: p = h->f[4] + above; break;
+        default: return fail(h, FDTD_B200_EINVAL, "unknown halo plane selector");
+    }
+    *device_ptr = p;
+    if (n_floats) *n_floats = h->plane;
+    return FDTD_B200_OK;
+}
+
+// ---- field access ----------------------------------------------------------------------------------
+
+int fdtd_b200_read_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (component != FDTD_B200_FIELD_E && component != FDTD_B200_FIELD_H) return fail(h, FDTD_B200_EINVAL, "component must be E or H");
+    BoxView B{};
+    size_t n = 0;
+    if (int rc = make_box(h, lo, hi, &B, &n)) return rc;
+    if (n == 0) return FDTD_B200_OK;
+    if (!out) return fail(h, FDTD_B200_EINVAL, "NULL output buffer");
+    if (int rc = set_device(h)) return rc;
+    const int c0 = component == FDTD_B200_FIELD_E ? 0 : 3;
+    // stage at most 16 Mi cells at a time, whole z-planes of the box
+    const size_t plane_cells = static_cast<size_t>(B.bx) * B.by;
+    const int planes_per = static_cast<int>(std::max<size_t>(1, (size_t(1) << 24) / plane_cells));
+    if (int rc = ensure_stage(h, std::min<size_t>(n, plane_cells * planes_per) * 3)) return rc;
+    for (int z = 0; z < B.bz; z += planes_per) {
+        BoxView S = B;
+        S.z0 = B.z0 + z;
+        S.bz = std::min(planes_per, B.bz - z);
+        const size_t cells = plane_cells * S.bz;
+        const int blocks = static_cast<int>(std::min<size_t>((cells + 255) / 256, 148 * 16));
+        k_gather_box<<<blocks, 256, 0, h->stream>>>(h->f[c0], h->f[c0 + 1], h->f[c0 + 2], S, h->d_stage);
+        h->launches += 1;
+        CU_TRY(h, cudaGetLastError());
+        CU_TRY(h, cudaMemcpyAsync(out + plane_cells * z * 3, h->d_stage, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CU_TRY(h, cudaStreamSynchronize(h->stream));
+    }
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], const float* in) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (component != FDTD_B200_FIELD_E && component != FDTD_B200_FIELD_H) return fail(h, FDTD_B200_EINVAL, "component must be E or H");
+    BoxView B{};
+    size_t n = 0;
+    if (int rc = make_box(h, lo, hi, &B, &n)) return rc;
+    if (n == 0) return FDTD_B200_OK;
+    if (!in) return fail(h, FDTD_B200_EINVAL, "NULL input buffer");
+    if (int rc = set_device(h)) return rc;
+    const int c0 = component == FDTD_B200_FIELD_E ? 0 : 3;
+    const size_t plane_cells = static_cast<size_t>(B.bx) * B.by;
+    const int planes_per = static_cast<int>(std::max<size_t>(1, (size_t(1) << 24) / plane_cells));
+    if (int rc = ensure_stage(h, std::min<size_t>(n, plane_cells * planes_per) * 3)) return rc;
+    for (int z = 0; z < B.bz; z += planes_per) {
+        BoxView S = B;
+        S.z0 = B.z0 + z;
+        S.bz = std::min(planes_per, B.bz - z);
+        const size_t cells = plane_cells * S.bz;
+        CU_TRY(h, cudaMemcpyAsync(h->d_stage, in + plane_cells * z * 3, cells * 3 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        const int blocks = static_cast<int>(std::min<size_t>((cells + 255) / 256, 148 * 16));
+        k_scatter_box<<<blocks, 256, 0, h->stream>>>(h->f[c0], h->f[c0 + 1], h->f[c0 + 2], S, h->d_stage);
+        h->launches += 1;
+        CU_TRY(h, cudaGetLastError());
+        CU_TRY(h, cudaStreamSynchronize(h->stream));
+    }
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_device_field(fdtd_b200_handle h, int c, void** device_ptr) {
+    if (!h || !device_ptr || c < 0 || c > 5) return fail(h, FDTD_B200_EINVAL, "bad component");
+    *device_ptr = h->f[c];
+    return FDTD_B200_OK;
+}
+
+// ---- probes ----------------------------------------------------------------------------------------
+
+int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* cells) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->d_probe_cells) { cudaFree(h->d_probe_cells); h->d_probe_cells = nullptr; }
+    if (h->d_probe_slot) { cudaFree(h->d_probe_slot); h->d_probe_slot = nullptr; }
+    if (h->d_probe_ring) { cudaFree(h->d_probe_ring); h->d_probe_ring = nullptr; }
+    h->n_probes_total = 0; h->n_probes_local = 0;
+    h->probe_first_tick = h->tick;
+    if (n == 0) return FDTD_B200_OK;
+    if (!cells) return fail(h, FDTD_B200_EINVAL, "NULL cells");
+    const uint64_t n_global = h->plane * h->nz;
+    const uint64_t base = h->z_begin * h->plane;
+    std::vector<std::pair<long long, int>> loc;
+    for (uint32_t k = 0; k < n; ++k) {
+        if (cells[k] >= n_global) return fail(h, FDTD_B200_EINVAL, "probe cell outside the lattice");
+        if (cells[k] >= base && cells[k] < base + h->n_local) loc.emplace_back(static_cast<long long>(cells[k] - base), static_cast<int>(k));
+    }
+    std::sort(loc.begin(), loc.end());
+    // the fused sampler writes one slot per distinct cell; duplicates are resolved on readback
+    h->n_probes_total = n;
+    CU_TRY(h, cudaMalloc(&h->d_probe_ring, sizeof(float) * 6 * n * static_cast<size_t>(h->ring_steps)));
+    CU_TRY(h, cudaMemset(h->d_probe_ring, 0, sizeof(float) * 6 * n * static_cast<size_t>(h->ring_steps)));
+    if (!loc.empty()) {
+        std::vector<long long> lc(loc.size());
+        std::vector<int> slot(loc.size());
+        for (size_t q = 0; q < loc.size(); ++q) { lc[q] = loc[q].first; slot[q] = loc[q].second; }
+        CU_TRY(h, cudaMalloc(&h->d_probe_cells, sizeof(long long) * lc.size()));
+        CU_TRY(h, cudaMalloc(&h->d_probe_slot, sizeof(int) * slot.size()));
+        CU_TRY(h, cudaMemcpy(h->d_probe_cells, lc.data(), sizeof(long long) * lc.size(), cudaMemcpyHostToDevice));
+        CU_TRY(h, cudaMemcpy(h->d_probe_slot, slot.data(), sizeof(int) * slot.size(), cudaMemcpyHostToDevice));
+        h->n_probes_local = static_cast<uint32_t>(loc.size());
+    }
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_steps, float* out) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (n_steps == 0 || h->n_probes_total == 0) return FDTD_B200_OK;
+    if (!out) return fail(h, FDTD_B200_EINVAL, "NULL output buffer");
+    if (first_tick < h->probe_first_tick || first_tick + n_steps > h->tick) return fail(h, FDTD_B200_EINVAL, "probe range not sampled (yet)");
+    if (h->tick - first_tick > h->ring_steps) return fail(h, FDTD_B200_EINVAL, "probe range already overwritten in the ring");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
+    uint64_t done = 0;
+    while (done < n_steps) {
+        const uint64_t r = (first_tick + done) % h->ring_steps;
+        const uint64_t run = std::min<uint64_t>(n_steps - done, h->ring_steps - r);
+        CU_TRY(h, cudaMemcpy(out + done * row, h->d_probe_ring + r * row, run * row * sizeof(float), cudaMemcpyDeviceToHost));
+        done += run;
+    }
+    return FDTD_B200_OK;
+}
+
+// ---- projection ------------------------------------------------------------------------------------
+
+int fdtd_b200_project(fdtd_b200_handle h, int component, const float projection[16], const float color_map[16],
+                      int colormap_mode, uint32_t w, uint32_t hgt, uint8_t* out_rgba, int rgba_is_device) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (component != FDTD_B200_FIELD_E && component != FDTD_B200_FIELD_H) return fail(h, FDTD_B200_EINVAL, "component must be E or H");
+    if (!projection || !color_map || !out_rgba || w == 0 || hgt == 0) return fail(h, FDTD_B200_EINVAL, "bad projection arguments");
+    if (colormap_mode < 0 || colormap_mode > 2) return fail(h, FDTD_B200_EINVAL, "unknown colormap mode");
+    if (int rc = set_device(h)) return rc;
+    const int c0 = component == FDTD_B200_FIELD_E ? 0 : 3;
+    ProjectView V{};
+    V.fx = h->f[c0]; V.fy = h->f[c0 + 1]; V.fz = h->f[c0 + 2];
+    V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz_global = static_cast<int>(h->nz);
+    V.z_begin = static_cast<int>(h->z_begin); V.nz_local = static_cast<int>(h->nzl);
+    std::memcpy(V.proj, projection, sizeof V.proj);
+    std::memcpy(V.cmap, color_map, sizeof V.cmap);
+    V.mode = colormap_mode; V.w = static_cast<int>(w); V.h = static_cast<int>(hgt);
+    const size_t bytes = static_cast<size_t>(w) * hgt * 4;
+    uchar4* d_out = reinterpret_cast<uchar4*>(out_rgba);
+    if (!rgba_is_device) {
+        if (int rc = ensure_stage(h, (bytes + 3) / 4)) return rc;
+        d_out = reinterpret_cast<uchar4*>(h->d_stage);
+        CU_TRY(h, cudaMemcpyAsync(d_out, out_rgba, bytes, cudaMemcpyHostToDevice, h->stream));  // untouched pixels keep caller content
+    }
+    dim3 block(32, 8, 1), grid((w + 31) / 32, (hgt + 7) / 8, 1);
+    k_project_rgba8<<<grid, block, 0, h->stream>>>(V, d_out);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    if (!rgba_is_device) {
+        CU_TRY(h, cudaMemcpyAsync(out_rgba, d_out, bytes, cudaMemcpyDeviceToHost, h->stream));
+        CU_TRY(h, cudaStreamSynchronize(h->stream));
+    }
+    return FDTD_B200_OK;
+}
+
+}  // extern "C"

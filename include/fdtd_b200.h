@@ -1,0 +1,244 @@
+/*
+ * fdtd_b200 — C ABI of the B200-native (sm_100a) FDTD time-stepping engine that replaces
+ * cem-solver's `fdtd::cpu` / `fdtd::wgpu` backends behind the reference's solver traits
+ * (cem-solver/src/lib.rs:28-142, cem-solver/src/project.rs:75-151).
+ *
+ * Everything crossing this boundary is plain C: integers, doubles, host pointers and opaque
+ * handles.  No call aborts or throws; every call returns FDTD_B200_OK (0) or an error code and
+ * leaves a message retrievable through fdtd_b200_last_error().  There is no CPU fallback: when
+ * no CUDA device is usable fdtd_b200_create() fails with FDTD_B200_ECUDA.
+ *
+ * One handle = reference `Instance` + `State` merged (cpu/mod.rs:225-232, 299-307): it owns the
+ * material index lattice, the coefficient table, the six SoA fp32 field components, sources,
+ * probes, tick and time.  A handle is single-caller (the reference drives it from one "solver"
+ * thread, cem-app/src/solver/runner.rs:471) but may be created on one thread and used on another.
+ *
+ * Linear cell index = x + nx*(y + ny*z)   (cem-solver/src/fdtd/strider.rs:47-53, 147-154).
+ */
+#ifndef FDTD_B200_H
+#define FDTD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDTD_B200_ABI_VERSION 1
+
+typedef struct fdtd_b200_solver* fdtd_b200_handle;
+
+enum {
+    FDTD_B200_OK = 0,
+    FDTD_B200_EINVAL = 1, /* bad argument; an out-of-lattice source point maps to the reference's panic
+                             (cpu/mod.rs:392-396, wgpu/mod.rs:342-346) in the Rust shim */
+    FDTD_B200_ENOMEM = 2,
+    FDTD_B200_ECUDA = 3, /* CUDA runtime error or no usable device */
+    FDTD_B200_ESTATE = 4 /* call not valid in the handle's current state */
+};
+
+/* cem-solver/src/lib.rs:139-142 `FieldComponent` */
+enum { FDTD_B200_FIELD_E = 0, FDTD_B200_FIELD_H = 1 };
+
+/* fdtd_b200_config.flags */
+enum {
+    /* Arithmetic of update.wgsl:89,127 reproduced operation by operation: true division by dx, no
+       FMA contraction, `+ psi(=0)` kept.  Bit-identical to the fp32 oracle.  Without the flag the
+       kernels multiply by 1/dx and let the compiler contract to FMA (documented in DESIGN.md). */
+    FDTD_B200_EXACT_ARITHMETIC = 1u << 0,
+    /* Force the one-thread-per-cell kernels even when nx % 4 == 0 (debugging / bisecting). */
+    FDTD_B200_FORCE_GENERIC_KERNELS = 1u << 1
+};
+
+/* cem-solver/src/material.rs:105-116 (same field order). */
+typedef struct fdtd_b200_material {
+    double relative_permeability;  /* mu_r    */
+    double magnetic_conductivity;  /* sigma_m */
+    double relative_permittivity;  /* eps_r   */
+    double eletrical_conductivity; /* sigma (spelling as in the reference) */
+} fdtd_b200_material;
+
+/* cem-solver/src/material.rs:21-25 */
+typedef struct fdtd_b200_physical_constants {
+    double vacuum_permittivity;
+    double vacuum_permeability;
+} fdtd_b200_physical_constants;
+
+/* cem-solver/src/fdtd/util.rs:91-96 — derived in f64 ... */
+typedef struct fdtd_b200_update_coefficients {
+    double c_a, c_b, d_a, d_b;
+} fdtd_b200_update_coefficients;
+
+/* ... and cast once to fp32 for the device (wgpu/mod.rs:661-679). */
+typedef struct fdtd_b200_coefficients_f32 {
+    float c_a, c_b, d_a, d_b;
+} fdtd_b200_coefficients_f32;
+
+/* Replaces FdtdSolverConfig + Resolution (fdtd/mod.rs:18-22, 64-67).  Lattice dims are integers
+ * because `ceil(size/dx)` of inexact ratios is the caller's business (fdtd/mod.rs:25-29). */
+typedef struct fdtd_b200_config {
+    uint64_t nx, ny, nz; /* global lattice */
+    double dx[3];        /* Resolution::spatial */
+    double dt;           /* Resolution::temporal */
+    int32_t device;      /* CUDA device ordinal */
+    uint32_t flags;
+    /* z-slab owned by this handle: global planes [z_begin, z_end).  0,0 means the whole lattice.
+       A slab with z_begin > 0 / z_end < nz keeps one ghost plane below / above that the caller
+       (or fdtd_b200_exchange_*) fills from the neighbouring rank. */
+    uint64_t z_begin, z_end;
+    uint32_t probe_ring_steps; /* capacity of the probe ring in steps; 0 = default (4096) */
+    uint32_t reserved;
+} fdtd_b200_config;
+
+/* Per-step forcing of one cell ≙ `SourceData` (wgpu/mod.rs:617-624) with a 64-bit cell index
+ * (the reference's u32 index cannot address 2048^3).  j feeds the E half-step, m the H half-step
+ * of the same step (cpu/mod.rs:445-451, 487-493). */
+typedef struct fdtd_b200_source {
+    uint64_t cell; /* global linear index */
+    float j[3];
+    float m[3];
+} fdtd_b200_source;
+
+/* ---- library ------------------------------------------------------------------------------ */
+
+int fdtd_b200_abi_version(void);
+/* Number of CUDA devices visible (0 if none / no driver). */
+int fdtd_b200_device_count(void);
+/* Thread-local message of the last failing call made without a handle (create, helpers). */
+const char* fdtd_b200_global_error(void);
+
+/* ---- host-side model helpers (f64, no device needed) --------------------------------------- */
+
+/* `UpdateCoefficients::new` (fdtd/util.rs:99-128).  EINVAL where the reference's NaN asserts fire. */
+int fdtd_b200_update_coefficients_new(double dt, const fdtd_b200_physical_constants* constants,
+                                      const fdtd_b200_material* material, fdtd_b200_update_coefficients* out);
+
+/* The per-cell coefficient buffer compressed into index + table (README.md:25-28 TODO).
+ * `materials` holds one record per cell (n_cells) in linear-index order — what the reference's
+ * per-cell `DomainDescription::material(point)` loop yields (cpu/mod.rs:244-264).  Ids are handed
+ * out in first-occurrence order, key = bit pattern of the four doubles.  ids_out: n_cells u32.
+ * palette_out: up to palette_cap records.  *n_palette_out: number of distinct materials (may
+ * exceed palette_cap; then only the first palette_cap are written and EINVAL is returned). */
+int fdtd_b200_index_materials(const fdtd_b200_material* materials, uint64_t n_cells, uint32_t* ids_out,
+                              fdtd_b200_material* palette_out, uint32_t palette_cap, uint32_t* n_palette_out);
+
+/* Same canonical numbering starting from an already-indexed lattice (ids_in may be any labelling
+ * of `palette_in`; equal materials under different labels are merged).  ids_in/ids_out may alias. */
+int fdtd_b200_canonicalize_material_index(const uint32_t* ids_in, uint64_t n_cells, const fdtd_b200_material* palette_in,
+                                          uint32_t n_palette_in, uint32_t* ids_out, fdtd_b200_material* palette_out,
+                                          uint32_t palette_cap, uint32_t* n_palette_out);
+
+/* `SolverBackend::memory_required` (lib.rs:41-44; cpu/mod.rs:217-221; wgpu/mod.rs:129-133): device
+ * bytes a handle for `cfg` will allocate with an index of `index_bytes` (1 or 2) per cell. */
+size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_bytes);
+
+/* ---- instance / state ---------------------------------------------------------------------- */
+
+/* `SolverBackend::create_instance` + `SolverInstance::create_state` (lib.rs:28-45, 70-79).
+ * material_ids: host, one u32 per cell of THIS handle's slab ([z_begin,z_end) planes, x fastest);
+ * NULL = every cell uses palette[0].  The device copy is u8 when n_palette <= 256, else u16
+ * (n_palette <= 65536).  Coefficients are derived in f64 and cast once to fp32. */
+int fdtd_b200_create(const fdtd_b200_config* cfg, const fdtd_b200_physical_constants* constants,
+                     const fdtd_b200_material* palette, uint32_t n_palette, const uint32_t* material_ids,
+                     fdtd_b200_handle* out);
+/* Same, from a caller-built fp32 coefficient table. */
+int fdtd_b200_create_from_table(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
+                                const uint32_t* material_ids, fdtd_b200_handle* out);
+void fdtd_b200_destroy(fdtd_b200_handle h);
+const char* fdtd_b200_last_error(fdtd_b200_handle h);
+
+/* A fresh `create_state` (cpu/mod.rs:310-322): zero fields, clear sources, tick = 0, time = 0. */
+int fdtd_b200_reset(fdtd_b200_handle h);
+/* Run subsequent work on this CUDA stream (a cudaStream_t; NULL restores the handle's own). */
+int fdtd_b200_set_stream(fdtd_b200_handle h, void* cuda_stream);
+int fdtd_b200_sync(fdtd_b200_handle h);
+
+/* `Time` (lib.rs:92-95).  time is accumulated `time += dt` in f64 (cpu/mod.rs:513). */
+uint64_t fdtd_b200_tick(fdtd_b200_handle h);
+double fdtd_b200_time(fdtd_b200_handle h);
+
+/* Introspection used by tests and the bench. */
+int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
+int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */
+uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h); /* kernels launched so far by this handle */
+/* Device copy of the material index back to the host as u32 (slab order). */
+int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out);
+int fdtd_b200_read_coefficient_table(fdtd_b200_handle h, fdtd_b200_coefficients_f32* out, uint32_t cap, uint32_t* n_out);
+
+/* ---- update pass --------------------------------------------------------------------------- */
+
+/* `begin_update` + `set_forcing`* (cpu/mod.rs:370-409): the forcing of the NEXT step only.  Later
+ * entries for the same cell win (CPU backend semantics).  Cells are global linear indices; entries
+ * outside the lattice → EINVAL and nothing is registered; entries outside this handle's slab are
+ * ignored.  Cleared after the step, like the reference clears `source_field`. */
+int fdtd_b200_set_sources(fdtd_b200_handle h, uint32_t n, const fdtd_b200_source* sources);
+
+/* Batched forcing for fdtd_b200_step(h, n>1): values[s][k][0..2] = j, [3..5] = m of source k at the
+ * s-th step from now; row s is consumed by the s-th following step; steps beyond n_steps run
+ * unforced.  Duplicate cells: the later column wins.  n_src = 0 clears the table. */
+int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_t* cells, uint64_t n_steps,
+                               const float* values);
+
+/* `UpdatePass::finish` × n (cpu/mod.rs:416-515): H half-step, E half-step on the new H, tick += 1,
+ * time += dt.  Enqueues and returns; errors surface at the next blocking call.  On a slab handle
+ * this does NOT exchange halos — use the phase calls below or fdtd_b200_step with a single slab. */
+int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps);
+
+/* Phases of one step for slab-decomposed runs: update local planes [z_lo, z_hi) of H or E. */
+int fdtd_b200_update_h(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
+int fdtd_b200_update_e(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
+/* tick += 1, time += dt, consume one forcing row, advance the probe ring. */
+int fdtd_b200_end_step(fdtd_b200_handle h);
+
+/* Halo planes (device pointers, nx*ny floats each).  which: */
+enum {
+    FDTD_B200_HALO_SEND_EX_TOP = 0, /* last owned plane of Ex — goes up after the E half-step */
+    FDTD_B200_HALO_SEND_EY_TOP = 1,
+    FDTD_B200_HALO_RECV_EX_LOW = 2, /* ghost plane below plane 0 */
+    FDTD_B200_HALO_RECV_EY_LOW = 3,
+    FDTD_B200_HALO_SEND_HX_BOTTOM = 4, /* first owned plane of Hx — goes down after the H half-step */
+    FDTD_B200_HALO_SEND_HY_BOTTOM = 5,
+    FDTD_B200_HALO_RECV_HX_HIGH = 6, /* ghost plane above the last plane */
+    FDTD_B200_HALO_RECV_HY_HIGH = 7
+};
+int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint64_t* n_floats);
+
+/* ---- field access -------------------------------------------------------------------------- */
+
+/* `Field::field(...).iter()` over the half-open box [lo, hi) in GLOBAL coordinates clipped to the
+ * lattice (lib.rs:97-136, util.rs:140-209): out receives (hi-lo) cells × 3 floats, xyz
+ * interleaved, x fastest — the fresh field (buffer tick%2, cpu/mod.rs:538).  The box must lie in
+ * this handle's slab.  Blocks until the data is on the host. */
+int fdtd_b200_read_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out);
+/* The inverse (≙ FieldMut, lib.rs:114-127): overwrite a box of E or H. */
+int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], const float* in);
+/* Raw device pointer of one scalar component c in 0..5 = Ex,Ey,Ez,Hx,Hy,Hz (first owned plane). */
+int fdtd_b200_device_field(fdtd_b200_handle h, int c, void** device_ptr);
+
+/* Probe sampling fused into the E half-step: after every step, E and H of each registered cell
+ * (global linear index) are appended to a device ring.  Re-registering clears the ring. */
+int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* cells);
+/* out[s][k][0..2] = E, [3..5] = H of probe k after step (first_tick + s + 1) was completed, i.e. the
+ * sample taken when tick went from first_tick+s to first_tick+s+1.  Probes outside this slab read
+ * as zeros.  EINVAL if the range has been overwritten in the ring or is not complete yet. */
+int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_steps, float* out);
+
+/* ---- projection ---------------------------------------------------------------------------- */
+
+enum {
+    FDTD_B200_COLORMAP_CPU = 0,    /* cpu/project.rs:117-165: uv=(x,y)/(w+1,h+1), M·(F,1), clamp, sRGB-encode */
+    FDTD_B200_COLORMAP_LINEAR = 1, /* project.wgsl:46-75 with the default body: pixel-centre uv, clamp(M·(F,1)) */
+    FDTD_B200_COLORMAP_APP_Z = 2   /* cem-app/src/solver/runner.rs:761-780: red/green on value.z */
+};
+/* `ProjectionPassAdd::add_projection` + `finish` (project.rs:112-133): renders the FRESH field into
+ * a w×h RGBA8 image.  projection / color_map: 4×4 column-major (nalgebra storage).  out_rgba is a
+ * host buffer of w*h*4 bytes (rgba_is_device = 0) or a device pointer (1).  The z-plane(s) sampled
+ * must lie inside this slab; pixels that fall outside it are left untouched. */
+int fdtd_b200_project(fdtd_b200_handle h, int component, const float projection[16], const float color_map[16],
+                      int colormap_mode, uint32_t w, uint32_t hgt, uint8_t* out_rgba, int rgba_is_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDTD_B200_H */
