@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""Benchmark of the FDTD time-stepping path (BASELINE.json metric: Yee cell-updates/s in Gcells/s).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--lattice nx,ny,nz]
+
+A "step" is one full leapfrog step (H half-step then E half-step, six components) of the whole lattice.
+N = 1 : BASELINE configs[2] — the 512^3 heterogeneous lattice inside the lossy absorbing layer (SURVEY §8d
+        config 3, the headline single-GPU roofline run).
+N > 1 : the same kind of lattice grown so every GPU keeps 512^3 cells (weak scaling), z-slab decomposed:
+        N=2 1024x512x512, N=4 1024x1024x512, N=8 1024^3; one-plane Hx,Hy / Ex,Ey halo per half-step over NCCL.
+`--impl reference` times the CPU restatement of the reference's own CPU backend (oracle/, f64 AoS, all host
+threads) on a bounded z-slab sample of the same lattice; the Rust reference itself cannot be built here.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_CELL_HALF_STEP = 37.0   # 6 fp32 reads + 3 fp32 writes + 1 B material index
+BYTES_PER_CELL_STEP = 74.0
+FALLBACK_HBM_GBS = 6650.0         # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def lattice_for(n_gpus: int) -> tuple:
+    return {1: (512, 512, 512), 2: (1024, 512, 512), 4: (1024, 1024, 512), 8: (1024, 1024, 1024)}.get(
+        n_gpus, (512, 512, 512 * n_gpus))
+
+
+def read_peak_hbm() -> tuple:
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.monotonic(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self, t0: float, t1: float):
+        sm, sm_max, reasons = [], [], set()
+        for t, line in self.rows:
+            if t < t0 or t > t1:
+                continue
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); sm_max.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(self.NAMES, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(sm_max), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(lattice, z_begin, z_end):
+    from fdtd_b200 import configs
+    from fdtd_b200.solver import GaussianPulse
+
+    pal = configs.heterogeneous_palette()
+    ids = configs.heterogeneous_slab_labels(lattice, z_begin, z_end)
+    nx, ny, nz = lattice
+    src = GaussianPulse(12.5, 2.5).with_amplitudes((0.0, 0.0, 50.0), (0.0, 0.0, 0.0))
+    sources = [((nx // 2, ny // 2, nz // 2), src)]
+    probes = [(nx // 2 + 16 * (k + 1), ny // 2, nz // 2) for k in range(4)] + [(nx // 2, ny // 2 + 16 * (k + 1), nz // 2) for k in range(4)]
+    w = configs.Workload(f"heterogeneous{nx}x{ny}x{nz}", tuple(lattice), configs.REDUCED_RES, configs.PhysicalConstants.REDUCED,
+                         pal, ids, sources, probes, 0)
+    return w
+
+
+def cpu_sample(lattice, planes: int):
+    """A z-slab sample of the benchmark lattice for the CPU legs: `planes` planes around the source plane."""
+    nx, ny, nz = lattice
+    z0 = max(nz // 2 - planes // 2, 0)
+    z1 = min(z0 + planes, nz)
+    return z0, z1
+
+
+def time_cpu_reference(lattice, planes: int, steps: int, warmup: int, threads=None) -> dict:
+    """Times the oracle's f64 restatement of FdtdCpuBackend (multi-threaded ≙ cpu/mod.rs:148-157) on a slab sample."""
+    import oracle
+    from fdtd_b200 import configs
+
+    oracle.build()
+    z0, z1 = cpu_sample(lattice, planes)
+    nx, ny, nz = lattice
+    sub = (nx, ny, z1 - z0)
+    ids = configs.heterogeneous_slab_labels(lattice, z0, z1)
+    pal = np.array([m.as_row() for m in configs.heterogeneous_palette()], dtype=np.float64)
+    cores = oracle.max_threads(fast=True) if threads is None else threads
+    oracle.set_threads(cores, fast=True)
+    s = oracle.RefSolver(sub, (1.0, 1.0, 1.0), 0.25, precision=oracle.F64, fast=True)
+    s.set_materials(pal, ids, 1.0, 1.0)
+    w = build_workload(lattice, z0, z1)
+    pts = [(nx // 2, ny // 2, nz // 2 - z0)]
+    tab = w.source_table(warmup + steps)
+    s.run(warmup, pts, tab[:warmup])
+    _, secs = s.run(steps, pts, tab[warmup:])
+    cells = nx * ny * (z1 - z0)
+    return {"value": cells * steps / secs / 1e9, "unit": "Gcells/s", "cores": int(cores), "kind": "port",
+            "sample": f"planes [{z0},{z1}) of the {nx}x{ny}x{nz} lattice ({cells} cells), {steps} steps, f64 AoS restatement of FdtdCpuBackend (oracle/), OpenMP",
+            "seconds": secs, "ms_per_step": 1e3 * secs / steps}
+
+
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    lattice = tuple(args.lattice) if args.lattice else lattice_for(args.gpus)
+    cb = time_cpu_reference(lattice, args.cpu_planes, args.steps, args.warmup)
+    out = {"metric": "Yee cell-updates/sec", "value": cb["value"], "unit": "Gcells/s", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic", "impl": "reference",
+           "config": {"workload": f"heterogeneous {lattice[0]}x{lattice[1]}x{lattice[2]} lattice + 16-cell lossy layer (BASELINE configs[2] shape), CPU leg on a bounded z-slab sample",
+                      "lattice": list(lattice)},
+           "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+           "e2e": {"value": cb["value"], "unit": "Gcells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def run_b200(args) -> None:
+    import fdtd_b200
+    from fdtd_b200 import _lib as L
+    from fdtd_b200.distributed import CudaSlabEngine, SlabStepper, partition_z
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    n_gpus = args.gpus
+    if world != n_gpus and world > 1:
+        raise SystemExit(f"--gpus {n_gpus} but WORLD_SIZE={world}")
+    dist = None
+    torch = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    lattice = tuple(args.lattice) if args.lattice else lattice_for(n_gpus)
+    nx, ny, nz = lattice
+    z_begin, z_end = partition_z(nz, world)[rank]
+    w = build_workload(lattice, z_begin, z_end)
+    backend = fdtd_b200.FdtdB200Backend(device=local_rank, exact_arithmetic=args.exact, z_slab=(z_begin, z_end) if world > 1 else None)
+    inst = backend.create_instance(w.solver_config(), w.domain())
+    st = inst.create_state()
+    st.register_probes(w.probes)
+    stepper = None
+    if world > 1:
+        engine = CudaSlabEngine(st)
+        stepper = SlabStepper(engine, rank, world, overlap=not args.no_overlap)
+
+    def advance(n):
+        if stepper is None:
+            st.step(n)
+        else:
+            stepper.step(n)
+
+    def barrier():
+        st.sync()
+        if dist is not None:
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    K, W = args.steps, args.warmup
+    table = w.source_table(W + 2 * K + 8)
+    pts = w.source_points()
+
+    # ---- device-resident throughput: forcing table already in HBM, no host traffic in the timed region ----
+    st.set_source_table(pts, table)
+    advance(W)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    st.set_profiling(True)
+    launches0 = st.kernel_launches
+    barrier()
+    t0 = time.monotonic()
+    st.timer_start()
+    advance(K)
+    ms = st.timer_stop()
+    barrier()
+    t1 = time.monotonic()
+    launches = st.kernel_launches - launches0
+    prof = [st.profile(0), st.profile(1)]
+    st.set_profiling(False)
+    if rank == 0:
+        sampler.stop()
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    cells_total = nx * ny * nz
+    value = cells_total * K / (ms * 1e-3) / 1e9
+
+    # ---- end to end through the reference-facing update pass: per step the host hands over that step's forcing
+    #      (H2D), the engine steps once, and the step's probe samples come back to the host (D2H) ----
+    st.sync()
+    tick0 = st.tick()
+    tab32 = table.astype(np.float32)
+    cells_arr = np.array([w.cell(p) for p in pts], dtype=np.uint64)
+    n_src, n_pr = len(pts), len(w.probes)
+    src_arr = (L.Source * n_src)()
+    probe_out = np.zeros((1, n_pr, 6), dtype=np.float32)
+    import ctypes as C
+
+    lib = fdtd_b200.lib()
+    barrier()
+    e0 = time.perf_counter()
+    for s in range(K):
+        row = tab32[tick0 + s]
+        for k in range(n_src):
+            src_arr[k].cell = int(cells_arr[k])
+            src_arr[k].j = (C.c_float * 3)(*row[k, :3])
+            src_arr[k].m = (C.c_float * 3)(*row[k, 3:])
+        L.check(lib.fdtd_b200_set_sources(st._h, n_src, src_arr), st._h)
+        advance(1)
+        L.check(lib.fdtd_b200_read_probes(st._h, tick0 + s, 1, probe_out.ctypes.data_as(C.POINTER(C.c_float))), st._h)
+    barrier()
+    e2e_s = time.perf_counter() - e0
+    if dist is not None:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = cells_total * K / e2e_s / 1e9
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = read_peak_hbm()
+    # dominant kernel = the slower of the two half-step kernels (each moves 37 B per cell it updates)
+    kern = []
+    for which, name in ((0, "update_h"), (1, "update_e")):
+        tot_ms, n_l, n_cells = prof[which]
+        if n_l:
+            kern.append({"kernel": name, "avg_ms": tot_ms / n_l, "launches": int(n_l),
+                         "achieved": BYTES_PER_CELL_HALF_STEP * n_cells / (tot_ms * 1e-3) / 1e9})
+    dom = min(kern, key=lambda k: k["achieved"])
+    roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["achieved"] / peak,
+                "traffic": None, "kernel": dom["kernel"], "kernel_avg_ms": dom["avg_ms"], "peak_source": peak_src,
+                "algorithmic_bytes_per_cell_half_step": BYTES_PER_CELL_HALF_STEP,
+                "step_achieved_gbs": BYTES_PER_CELL_STEP * value * (1.0 / n_gpus), "step_frac": BYTES_PER_CELL_STEP * value / n_gpus / peak,
+                "kernels": kern}
+    cpu_baseline = None
+    if n_gpus == 1 and not args.no_cpu_baseline:
+        cb = time_cpu_reference(lattice, args.cpu_planes, args.cpu_steps, 2)
+        cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    out = {"metric": "Yee cell-updates/sec", "value": value, "unit": "Gcells/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
+           "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"heterogeneous {nx}x{ny}x{nz} lattice (64 balls of 4 material kinds) inside the 16-cell graded lossy layer, "
+                                  "Gaussian point source, 8 probes (BASELINE configs[2]; weak-scaled 512^3 cells per GPU for N>1)",
+                      "lattice": [nx, ny, nz], "cells_per_gpu": cells_total // n_gpus, "decomposition": f"z-slabs x{n_gpus}",
+                      "l2": "working set 25 B/cell x 134M cells per GPU >> 126 MB L2 (no flush needed)",
+                      "arithmetic": "exact" if args.exact else "fast", "halo_overlap": bool(world > 1 and not args.no_overlap)},
+           "roofline": roofline, "cpu_baseline": cpu_baseline,
+           "e2e": {"value": e2e_value, "unit": "Gcells/s", "h2d_bytes_per_step": 32 * n_src, "d2h_bytes_per_step": 24 * n_pr,
+                   "ms_per_step": 1e3 * e2e_s / K},
+           "gpu_launches": int(launches), "clocks": sampler.summary(t0, t1)}
+    print(json.dumps(out), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=("b200", "reference"), default="b200")
+    ap.add_argument("--lattice", type=lambda s: [int(v) for v in s.split(",")], default=None)
+    ap.add_argument("--exact", action="store_true", help="FDTD_B200_EXACT_ARITHMETIC kernels")
+    ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-planes", type=int, default=32, help="z-planes in the CPU legs' sample slab")
+    ap.add_argument("--cpu-steps", type=int, default=10)
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -68,6 +68,10 @@ SYMBOLS = {
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
     "fdtd_b200_kernel_launches": (C.c_uint64, [_H]),
+    "fdtd_b200_set_profiling": (C.c_int, [_H, C.c_int]),
+    "fdtd_b200_get_profile": (C.c_int, [_H, C.c_int, C.POINTER(C.c_double), _u64p, _u64p]),
+    "fdtd_b200_timer_start": (C.c_int, [_H]),
+    "fdtd_b200_timer_stop": (C.c_int, [_H, C.POINTER(C.c_double)]),
     "fdtd_b200_read_material_ids": (C.c_int, [_H, _u32p]),
     "fdtd_b200_read_coefficient_table": (C.c_int, [_H, C.POINTER(CoefficientsF32), C.c_uint32, _u32p]),
     "fdtd_b200_set_sources": (C.c_int, [_H, C.c_uint32, C.POINTER(Source)]),
@@ -77,6 +81,7 @@ SYMBOLS = {
     "fdtd_b200_update_e": (C.c_int, [_H, C.c_uint64, C.c_uint64]),
     "fdtd_b200_end_step": (C.c_int, [_H]),
     "fdtd_b200_halo_plane": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p), _u64p]),
+    "fdtd_b200_halo_copy": (C.c_int, [_H, C.c_int, _H, C.c_int]),
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_write_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_device_field": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p)]),

@@ -68,6 +68,11 @@ struct fdtd_b200_solver {
     uint64_t tick = 0;
     double time = 0.0;
     uint64_t launches = 0;
+    // per-kernel CUDA-event profiling (bench.py roofline) and a stream timer
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[2];  // [0]=H launches, [1]=E launches
+    uint64_t prof_cells[2] = {0, 0};
+    cudaEvent_t timer_start = nullptr, timer_stop = nullptr;
     Tune tune;
     std::string err;
 };
@@ -269,17 +274,49 @@ int launch_e_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     return FDTD_B200_OK;
 }
 
+int prof_begin(fdtd_b200_handle h, int which, int planes) {
+    if (!h->profiling) return FDTD_B200_OK;
+    cudaEvent_t a, b;
+    CU_TRY(h, cudaEventCreate(&a));
+    CU_TRY(h, cudaEventCreate(&b));
+    h->prof_events[which].emplace_back(a, b);
+    h->prof_cells[which] += static_cast<uint64_t>(planes) * h->plane;
+    CU_TRY(h, cudaEventRecord(a, h->stream));
+    return FDTD_B200_OK;
+}
+int prof_end(fdtd_b200_handle h, int which) {
+    if (!h->profiling) return FDTD_B200_OK;
+    CU_TRY(h, cudaEventRecord(h->prof_events[which].back().second, h->stream));
+    return FDTD_B200_OK;
+}
+
 int launch_h(fdtd_b200_handle h, int z_lo, int z_hi) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
     const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
-    if (h->idx_bytes == 1) return exact ? launch_h_t<true, uint8_t>(h, z_lo, z_hi) : launch_h_t<false, uint8_t>(h, z_lo, z_hi);
-    return exact ? launch_h_t<true, uint16_t>(h, z_lo, z_hi) : launch_h_t<false, uint16_t>(h, z_lo, z_hi);
+    if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
+    int rc;
+    if (h->idx_bytes == 1) rc = exact ? launch_h_t<true, uint8_t>(h, z_lo, z_hi) : launch_h_t<false, uint8_t>(h, z_lo, z_hi);
+    else rc = exact ? launch_h_t<true, uint16_t>(h, z_lo, z_hi) : launch_h_t<false, uint16_t>(h, z_lo, z_hi);
+    if (rc) return rc;
+    return prof_end(h, 0);
 }
 int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
     const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
-    if (h->idx_bytes == 1) return exact ? launch_e_t<true, uint8_t>(h, z_lo, z_hi) : launch_e_t<false, uint8_t>(h, z_lo, z_hi);
-    return exact ? launch_e_t<true, uint16_t>(h, z_lo, z_hi) : launch_e_t<false, uint16_t>(h, z_lo, z_hi);
+    if (int rc = prof_begin(h, 1, z_hi - z_lo)) return rc;
+    int rc;
+    if (h->idx_bytes == 1) rc = exact ? launch_e_t<true, uint8_t>(h, z_lo, z_hi) : launch_e_t<false, uint8_t>(h, z_lo, z_hi);
+    else rc = exact ? launch_e_t<true, uint16_t>(h, z_lo, z_hi) : launch_e_t<false, uint16_t>(h, z_lo, z_hi);
+    if (rc) return rc;
+    return prof_end(h, 1);
+}
+
+void prof_clear(fdtd_b200_handle h) {
+    for (int w = 0; w < 2; ++w) {
+        for (auto& ev : h->prof_events[w]) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+        h->prof_events[w].clear();
+        h->prof_cells[w] = 0;
+    }
 }
 
 void end_step(fdtd_b200_handle h) {
@@ -538,6 +575,9 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_probe_slot) cudaFree(h->d_probe_slot);
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
     if (h->d_stage) cudaFree(h->d_stage);
+    prof_clear(h);
+    if (h->timer_start) cudaEventDestroy(h->timer_start);
+    if (h->timer_stop) cudaEventDestroy(h->timer_stop);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     (void)cudaGetLastError();
     delete h;
@@ -579,6 +619,52 @@ double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
 int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }
 int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h) { return h ? h->launches : 0; }
+
+int fdtd_b200_set_profiling(fdtd_b200_handle h, int enabled) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    prof_clear(h);
+    h->profiling = enabled != 0;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_get_profile(fdtd_b200_handle h, int which, double* total_ms, uint64_t* n_launches, uint64_t* n_cells) {
+    if (!h || which < 0 || which > 1) return fail(h, FDTD_B200_EINVAL, "which must be 0 (H) or 1 (E)");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    double ms = 0.0;
+    for (auto& ev : h->prof_events[which]) {
+        float t = 0.f;
+        CU_TRY(h, cudaEventElapsedTime(&t, ev.first, ev.second));
+        ms += t;
+    }
+    if (total_ms) *total_ms = ms;
+    if (n_launches) *n_launches = h->prof_events[which].size();
+    if (n_cells) *n_cells = h->prof_cells[which];
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_timer_start(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    if (!h->timer_start) { CU_TRY(h, cudaEventCreate(&h->timer_start)); CU_TRY(h, cudaEventCreate(&h->timer_stop)); }
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    CU_TRY(h, cudaEventRecord(h->timer_start, h->stream));
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_timer_stop(fdtd_b200_handle h, double* elapsed_ms) {
+    if (!h || !elapsed_ms) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    if (!h->timer_start) return fail(h, FDTD_B200_ESTATE, "timer_stop without timer_start");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaEventRecord(h->timer_stop, h->stream));
+    CU_TRY(h, cudaEventSynchronize(h->timer_stop));
+    float t = 0.f;
+    CU_TRY(h, cudaEventElapsedTime(&t, h->timer_start, h->timer_stop));
+    *elapsed_ms = t;
+    return FDTD_B200_OK;
+}
 
 int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out) {
     if (!h || !ids_out) return fail(h, FDTD_B200_EINVAL, "NULL argument");
@@ -728,6 +814,33 @@ int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint6
     }
     *device_ptr = p;
     if (n_floats) *n_floats = h->plane;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle src, int which_src) {
+    if (!dst || !src) return fail(dst, FDTD_B200_EINVAL, "NULL handle");
+    if (dst->plane != src->plane) return fail(dst, FDTD_B200_EINVAL, "halo planes differ in size");
+    void* pd = nullptr; void* ps = nullptr;
+    if (int rc = fdtd_b200_halo_plane(dst, which_dst, &pd, nullptr)) return rc;
+    if (int rc = fdtd_b200_halo_plane(src, which_src, &ps, nullptr)) return rc;
+    // order: src stream → event → dst stream
+    cudaEvent_t ev;
+    CU_TRY(src, cudaSetDevice(src->device));
+    CU_TRY(src, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    CU_TRY(src, cudaEventRecord(ev, src->stream));
+    CU_TRY(dst, cudaSetDevice(dst->device));
+    CU_TRY(dst, cudaStreamWaitEvent(dst->stream, ev, 0));
+    const size_t bytes = static_cast<size_t>(dst->plane) * sizeof(float);
+    if (dst->device == src->device) CU_TRY(dst, cudaMemcpyAsync(pd, ps, bytes, cudaMemcpyDeviceToDevice, dst->stream));
+    else CU_TRY(dst, cudaMemcpyPeerAsync(pd, dst->device, ps, src->device, bytes, dst->stream));
+    // the source plane must not be overwritten before the copy has run: src waits for it
+    cudaEvent_t done;
+    CU_TRY(dst, cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    CU_TRY(dst, cudaEventRecord(done, dst->stream));
+    CU_TRY(src, cudaSetDevice(src->device));
+    CU_TRY(src, cudaStreamWaitEvent(src->stream, done, 0));
+    cudaEventDestroy(ev);
+    cudaEventDestroy(done);
     return FDTD_B200_OK;
 }
 

@@ -1,0 +1,159 @@
+"""z-slab decomposition of the lattice over ranks (one process per GPU) and the one-plane E/H halo
+exchange per half-step.  torch.distributed is plumbing only: NCCL send/recv between
+z-neighbours, no collective on the data path.
+
+Dependencies of the Yee update across a slab boundary (update.wgsl:147-177):
+  H half-step of rank r needs Ex,Ey of plane z_begin-1      → after each E half-step every rank sends
+                                                              its TOP Ex,Ey plane UP;
+  E half-step of rank r needs the new Hx,Hy of plane z_end  → after each H half-step every rank sends
+                                                              its BOTTOM Hx,Hy plane DOWN.
+The boundary plane is updated first, its send is started, and the interior planes are updated while
+the message is in flight.
+
+The stepper is written against a small "slab engine" protocol (update_h, update_e, end_step, halo
+tensors) so the orchestration is testable on CPU with gloo (tests/test_distributed_cpu.py).
+"""
+from __future__ import annotations
+
+from typing import Optional, Protocol, Sequence
+
+import numpy as np
+
+
+def partition_z(nz: int, world: int) -> list:
+    """Contiguous balanced z-slabs [(z_begin, z_end)] — earlier ranks take the remainder planes."""
+    if world < 1 or nz < world:
+        raise ValueError(f"cannot split {nz} planes over {world} ranks")
+    base, rem = divmod(nz, world)
+    out, z = [], 0
+    for r in range(world):
+        n = base + (1 if r < rem else 0)
+        out.append((z, z + n))
+        z += n
+    return out
+
+
+class SlabEngine(Protocol):
+    n_planes: int
+
+    def update_h(self, z_lo: int, z_hi: int) -> None: ...
+    def update_e(self, z_lo: int, z_hi: int) -> None: ...
+    def end_step(self) -> None: ...
+    def halo(self, name: str):  # torch tensor; names: send_e_top, recv_e_low, send_h_bottom, recv_h_high
+        ...
+
+
+class CudaHaloView:
+    """Exposes a device plane of the C library as a torch tensor without copying (__cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, n_floats: int):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+class CudaSlabEngine:
+    """SlabEngine over a FdtdB200SolverState that owns planes [z_begin, z_end) on this rank's GPU."""
+
+    def __init__(self, state, device=None):
+        import torch
+
+        from . import _lib as L
+
+        self.state = state
+        self.n_planes = state.z_end - state.z_begin
+        self._torch = torch
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        state.set_stream(torch.cuda.current_stream(dev).cuda_stream)  # NCCL orders against torch's current stream
+
+        def planes(a: int, b: int):
+            out = []
+            for which in (a, b):
+                ptr, n = state.halo_plane(which)
+                out.append(torch.as_tensor(CudaHaloView(ptr, n), device=dev))
+            return out
+
+        # two components per message (Ex,Ey / Hx,Hy) live in separate SoA arrays → two tensors each
+        self._halo = {
+            "send_e_top": planes(L.HALO_SEND_EX_TOP, L.HALO_SEND_EY_TOP),
+            "recv_e_low": planes(L.HALO_RECV_EX_LOW, L.HALO_RECV_EY_LOW),
+            "send_h_bottom": planes(L.HALO_SEND_HX_BOTTOM, L.HALO_SEND_HY_BOTTOM),
+            "recv_h_high": planes(L.HALO_RECV_HX_HIGH, L.HALO_RECV_HY_HIGH),
+        }
+
+    def update_h(self, z_lo: int, z_hi: int) -> None:
+        self.state.update_h(z_lo, z_hi)
+
+    def update_e(self, z_lo: int, z_hi: int) -> None:
+        self.state.update_e(z_lo, z_hi)
+
+    def end_step(self) -> None:
+        self.state.end_step()
+
+    def halo(self, name: str):
+        return self._halo[name]
+
+
+class SlabStepper:
+    """Leapfrog step of one rank's slab with neighbour halo exchange over torch.distributed."""
+
+    def __init__(self, engine: SlabEngine, rank: int, world: int, group=None, overlap: bool = True):
+        self.engine, self.rank, self.world, self.group, self.overlap = engine, rank, world, group, overlap
+        self.lower: Optional[int] = rank - 1 if rank > 0 else None
+        self.upper: Optional[int] = rank + 1 if rank + 1 < world else None
+        self.exchanges = 0
+
+    # -- transport -----------------------------------------------------------------------------
+    def _start(self, send_name: str, send_to: Optional[int], recv_name: str, recv_from: Optional[int]):
+        import torch.distributed as dist
+
+        ops = []
+        # post receives first, lowest peer first on every rank → the pairing is deadlock-free for any backend
+        if recv_from is not None:
+            for t in self.engine.halo(recv_name):
+                ops.append(dist.P2POp(dist.irecv, t, recv_from, self.group))
+        if send_to is not None:
+            for t in self.engine.halo(send_name):
+                ops.append(dist.P2POp(dist.isend, t, send_to, self.group))
+        if not ops:
+            return []
+        self.exchanges += 1
+        return dist.batch_isend_irecv(ops)
+
+    @staticmethod
+    def _finish(works) -> None:
+        for w in works:
+            w.wait()
+
+    def start_h_exchange(self):
+        """After the H half-step: bottom Hx,Hy go DOWN, ghost-above comes from the upper rank."""
+        return self._start("send_h_bottom", self.lower, "recv_h_high", self.upper)
+
+    def start_e_exchange(self):
+        """After the E half-step: top Ex,Ey go UP, ghost-below comes from the lower rank."""
+        return self._start("send_e_top", self.upper, "recv_e_low", self.lower)
+
+    def refresh_halos(self) -> None:
+        """Make ghost planes consistent after fields were written from outside (write_field)."""
+        self._finish(self.start_h_exchange())
+        self._finish(self.start_e_exchange())
+
+    # -- stepping ------------------------------------------------------------------------------
+    def step(self, n_steps: int = 1) -> None:
+        e, n = self.engine, self.engine.n_planes
+        for _ in range(n_steps):
+            if self.overlap and n > 1:
+                # H: the bottom plane feeds the lower rank — do it first, ship it, then the rest
+                e.update_h(0, 1)
+                works = self.start_h_exchange()
+                e.update_h(1, n)
+                self._finish(works)
+                # E: the top plane needs the ghost H just received and feeds the upper rank
+                e.update_e(n - 1, n)
+                works = self.start_e_exchange()
+                e.update_e(0, n - 1)
+                self._finish(works)
+            else:
+                e.update_h(0, n)
+                self._finish(self.start_h_exchange())
+                e.update_e(0, n)
+                self._finish(self.start_e_exchange())
+            e.end_step()

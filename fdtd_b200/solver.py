@@ -393,6 +393,23 @@ class FdtdB200SolverState:
         b = (C.c_uint64 * 3)(*hi)
         L.check(self._lib.fdtd_b200_write_field(self._h, component, a, b, v.ctypes.data_as(C.POINTER(C.c_float))), self._h)
 
+    def set_profiling(self, enabled: bool) -> None:
+        L.check(self._lib.fdtd_b200_set_profiling(self._h, int(enabled)), self._h)
+
+    def profile(self, which: int) -> tuple:
+        """(total device ms, launches, cells updated) of the H (0) or E (1) half-step kernels."""
+        ms, n, cells = C.c_double(), C.c_uint64(), C.c_uint64()
+        L.check(self._lib.fdtd_b200_get_profile(self._h, which, C.byref(ms), C.byref(n), C.byref(cells)), self._h)
+        return ms.value, n.value, cells.value
+
+    def timer_start(self) -> None:
+        L.check(self._lib.fdtd_b200_timer_start(self._h), self._h)
+
+    def timer_stop(self) -> float:
+        ms = C.c_double()
+        L.check(self._lib.fdtd_b200_timer_stop(self._h, C.byref(ms)), self._h)
+        return ms.value
+
     def material_ids(self) -> np.ndarray:
         n = self.lattice
         out = np.zeros(n[0] * n[1] * (self.z_end - self.z_begin), dtype=np.uint32)

@@ -162,6 +162,15 @@ double fdtd_b200_time(fdtd_b200_handle h);
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
 int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h); /* kernels launched so far by this handle */
+/* Measurement: with profiling on, every H / E half-step launch is bracketed by CUDA events on the
+ * handle's stream.  get_profile(which = 0 H | 1 E) blocks and returns the summed device time, the
+ * number of launches and the cells they updated since profiling was switched on. */
+int fdtd_b200_set_profiling(fdtd_b200_handle h, int enabled);
+int fdtd_b200_get_profile(fdtd_b200_handle h, int which, double* total_ms, uint64_t* n_launches, uint64_t* n_cells);
+/* CUDA-event stopwatch on the handle's stream: start synchronises then records; stop records,
+ * waits and returns the device time between the two. */
+int fdtd_b200_timer_start(fdtd_b200_handle h);
+int fdtd_b200_timer_stop(fdtd_b200_handle h, double* elapsed_ms);
 /* Device copy of the material index back to the host as u32 (slab order). */
 int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out);
 int fdtd_b200_read_coefficient_table(fdtd_b200_handle h, fdtd_b200_coefficients_f32* out, uint32_t cap, uint32_t* n_out);
@@ -203,6 +212,10 @@ enum {
     FDTD_B200_HALO_RECV_HY_HIGH = 7
 };
 int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint64_t* n_floats);
+/* Single-process multi-GPU transport: copy halo plane `which_src` of `src` into `which_dst` of `dst`
+ * (cudaMemcpyPeerAsync over NVLink when the handles live on different devices), ordered after the
+ * work already enqueued on src's stream and before later work on dst's stream. */
+int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle src, int which_src);
 
 /* ---- field access -------------------------------------------------------------------------- */
 

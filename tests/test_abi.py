@@ -1,0 +1,160 @@
+"""CPU tests of the C-ABI shared library: it loads, exports every symbol include/fdtd_b200.h declares, and its
+host-side helpers (f64 coefficient derivation, material indexing) agree bit-for-bit with the oracle.  No compute
+calls are made here; on a machine without a GPU `create` must fail loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    txt = open(os.path.join(ROOT, "include", "fdtd_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(fdtd_b200_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_declared_symbol(b200):
+    from fdtd_b200 import _lib
+
+    lib = b200.lib()
+    names = header_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/fdtd_b200.h but not exported"
+    assert set(names) == set(_lib.SYMBOLS), "ctypes binding and header disagree"
+    assert lib.fdtd_b200_abi_version() == 1
+
+
+def test_struct_layouts(b200):
+    from fdtd_b200 import _lib as L
+
+    assert C.sizeof(L.Material) == 32 and C.sizeof(L.Source) == 32 and C.sizeof(L.CoefficientsF32) == 16
+    assert C.sizeof(L.Config) == 3 * 8 + 3 * 8 + 8 + 4 + 4 + 2 * 8 + 4 + 4
+
+
+def test_update_coefficients_match_oracle_bitwise(b200, oracle):
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        m = np.abs(rng.standard_normal(4)) + np.array([0.1, 0, 0.1, 0])
+        dt, eps0, mu0 = abs(rng.standard_normal()) + 0.01, 8.8541878188e-12, 1.25663706127e-6
+        out = L.UpdateCoefficients()
+        rc = lib.fdtd_b200_update_coefficients_new(dt, C.byref(L.PhysicalConstants(eps0, mu0)), C.byref(L.Material(*m)), C.byref(out))
+        assert rc == 0
+        ref = oracle.update_coefficients(dt, eps0, mu0, m)
+        assert [out.c_a, out.c_b, out.d_a, out.d_b] == ref.tolist()
+
+
+def test_update_coefficients_nan_is_an_error(b200):
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    out = L.UpdateCoefficients()
+    # perm = 0 and sigma = 0 → 0/0 = NaN: the reference asserts (util.rs:112-113)
+    rc = lib.fdtd_b200_update_coefficients_new(0.25, C.byref(L.PhysicalConstants(1.0, 1.0)), C.byref(L.Material(1.0, 0.0, 0.0, 0.0)), C.byref(out))
+    assert rc == L.EINVAL and b"NaN" in lib.fdtd_b200_global_error()
+
+
+def test_index_materials_matches_oracle(b200, oracle):
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    rng = np.random.default_rng(1)
+    pal = np.array([[1, 0, 1, 0], [1, 0, 3.9, 0], [2, 0.5, 1, 0], [1, 0, 1, 10], [1, 0, 1, -0.0]], dtype=np.float64)
+    lab = rng.integers(0, len(pal), 5000)
+    per_cell = np.ascontiguousarray(pal[lab])
+    ids = np.zeros(len(lab), dtype=np.uint32)
+    pal_out = (L.Material * 16)()
+    n = C.c_uint32()
+    rc = lib.fdtd_b200_index_materials(per_cell.ctypes.data_as(C.POINTER(L.Material)), len(lab), ids.ctypes.data_as(C.POINTER(C.c_uint32)), pal_out, 16, C.byref(n))
+    assert rc == 0
+    ref_ids, ref_pal = oracle.index_materials(per_cell)
+    assert n.value == len(ref_pal) == 5          # -0.0 and 0.0 conductivities are different bit patterns
+    assert np.array_equal(ids, ref_ids)          # integer material indexing: bit-exact
+    got_pal = np.array([[p.relative_permeability, p.magnetic_conductivity, p.relative_permittivity, p.eletrical_conductivity] for p in pal_out[: n.value]])
+    assert np.array_equal(got_pal.view(np.uint64), ref_pal.view(np.uint64))
+    # palette_cap too small → EINVAL, count still reported
+    rc = lib.fdtd_b200_index_materials(per_cell.ctypes.data_as(C.POINTER(L.Material)), len(lab), ids.ctypes.data_as(C.POINTER(C.c_uint32)), pal_out, 2, C.byref(n))
+    assert rc == L.EINVAL and n.value == 5
+
+
+def test_canonicalize_matches_per_cell_indexing(b200, oracle):
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    rng = np.random.default_rng(2)
+    pal = np.array([[1, 0, 1, 0], [1, 0, 3.9, 0], [1, 0, 1, 0], [2, 0.5, 1, 0]], dtype=np.float64)  # label 2 duplicates label 0
+    lab = rng.integers(0, 4, 3000).astype(np.uint32)
+    ids = np.zeros_like(lab)
+    pal_out = (L.Material * 8)()
+    n = C.c_uint32()
+    rc = lib.fdtd_b200_canonicalize_material_index(lab.ctypes.data_as(C.POINTER(C.c_uint32)), len(lab), pal.ctypes.data_as(C.POINTER(L.Material)), 4,
+                                                   ids.ctypes.data_as(C.POINTER(C.c_uint32)), pal_out, 8, C.byref(n))
+    assert rc == 0 and n.value == 3
+    ref_ids, _ = oracle.index_materials(pal[lab])
+    assert np.array_equal(ids, ref_ids)
+    bad = lab.copy(); bad[7] = 9
+    rc = lib.fdtd_b200_canonicalize_material_index(bad.ctypes.data_as(C.POINTER(C.c_uint32)), len(bad), pal.ctypes.data_as(C.POINTER(L.Material)), 4,
+                                                   ids.ctypes.data_as(C.POINTER(C.c_uint32)), pal_out, 8, C.byref(n))
+    assert rc == L.EINVAL
+
+
+def test_memory_required(b200):
+    cfg = b200.FdtdSolverConfig.from_lattice((512, 512, 512), b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED)
+    be = b200.FdtdB200Backend()
+    need = be.memory_required(cfg)
+    cells = 512 ** 3
+    assert need == 24 * 512 * 512 * 514 + cells + 16
+    assert need / cells < 26                      # vs 136 B/cell (cpu/mod.rs:217-221) and 80 B/cell (wgpu/mod.rs:129-133)
+    assert be.memory_required(cfg, 2) == need + cells
+    slab = b200.FdtdB200Backend(z_slab=(128, 256))
+    assert slab.memory_required(cfg) == 24 * 512 * 512 * 130 + 512 * 512 * 128 + 16
+
+
+def test_invalid_configs_are_rejected_without_a_device(b200):
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    cfg = L.Config()
+    cfg.nx, cfg.ny, cfg.nz = 4, 4, 0
+    cfg.dx = (C.c_double * 3)(1, 1, 1)
+    cfg.dt = 0.25
+    h = C.c_void_p()
+    pal = (L.Material * 1)(L.Material(1, 0, 1, 0))
+    pc = L.PhysicalConstants(1, 1)
+    assert lib.fdtd_b200_create(C.byref(cfg), C.byref(pc), pal, 1, None, C.byref(h)) == L.EINVAL
+    cfg.nz = 4
+    cfg.dx = (C.c_double * 3)(1, 0, 1)
+    assert lib.fdtd_b200_create(C.byref(cfg), C.byref(pc), pal, 1, None, C.byref(h)) == L.EINVAL
+    cfg.dx = (C.c_double * 3)(1, 1, 1)
+    cfg.z_begin, cfg.z_end = 3, 9
+    assert lib.fdtd_b200_create(C.byref(cfg), C.byref(pc), pal, 1, None, C.byref(h)) == L.EINVAL
+    assert h.value is None
+
+
+def test_no_cpu_fallback(b200):
+    """Without a CUDA device the product path must fail loudly (ECUDA), never compute on the host."""
+    from fdtd_b200 import _lib as L
+
+    if b200.lib().fdtd_b200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    cfg = b200.FdtdSolverConfig.from_lattice((8, 8, 8), b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED)
+    inst = b200.FdtdB200Backend().create_instance(cfg, b200.MaterialLattice([b200.Material.VACUUM]))
+    with pytest.raises(b200.Fdtd_b200Error) as ei:
+        inst.create_state()
+    assert ei.value.code == L.ECUDA and "no CPU fallback" in str(ei.value)
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "fdtd_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "fdtd_ref" not in txt, f
