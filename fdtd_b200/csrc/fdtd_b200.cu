@@ -180,42 +180,39 @@ using HKernel = void (*)(LatticeView, ForcingView, int, int, int);
 using EKernel = void (*)(LatticeView, ForcingView, ProbeView, int, int, int);
 
 struct Shape { int bx, by; };
-constexpr Shape kShapes[] = {{32, 4}, {32, 8}, {64, 2}, {64, 4}, {128, 1}, {128, 2}, {128, 4}};
+constexpr Shape kShapes[] = {{32, 4}, {64, 2}, {128, 1}, {128, 2}, {128, 4}};
 constexpr int kNumShapes = sizeof(kShapes) / sizeof(kShapes[0]);
 
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 HKernel h_kernel(int shape) {
     switch (shape) {
         case 0: return k_update_h_vec4<EXACT, IdxT, 32, 4>;
-        case 1: return k_update_h_vec4<EXACT, IdxT, 32, 8>;
-        case 2: return k_update_h_vec4<EXACT, IdxT, 64, 2>;
-        case 3: return k_update_h_vec4<EXACT, IdxT, 64, 4>;
-        case 4: return k_update_h_vec4<EXACT, IdxT, 128, 1>;
-        case 5: return k_update_h_vec4<EXACT, IdxT, 128, 2>;
+        case 1: return k_update_h_vec4<EXACT, IdxT, 64, 2>;
+        case 2: return k_update_h_vec4<EXACT, IdxT, 128, 1>;
+        case 3: return k_update_h_vec4<EXACT, IdxT, 128, 2>;
         default: return k_update_h_vec4<EXACT, IdxT, 128, 4>;
     }
 }
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 EKernel e_kernel(int shape) {
     switch (shape) {
         case 0: return k_update_e_vec4<EXACT, IdxT, 32, 4>;
-        case 1: return k_update_e_vec4<EXACT, IdxT, 32, 8>;
-        case 2: return k_update_e_vec4<EXACT, IdxT, 64, 2>;
-        case 3: return k_update_e_vec4<EXACT, IdxT, 64, 4>;
-        case 4: return k_update_e_vec4<EXACT, IdxT, 128, 1>;
-        case 5: return k_update_e_vec4<EXACT, IdxT, 128, 2>;
+        case 1: return k_update_e_vec4<EXACT, IdxT, 64, 2>;
+        case 2: return k_update_e_vec4<EXACT, IdxT, 128, 1>;
+        case 3: return k_update_e_vec4<EXACT, IdxT, 128, 2>;
         default: return k_update_e_vec4<EXACT, IdxT, 128, 4>;
     }
 }
 
 int pick_shape(fdtd_b200_handle h) {
+    // 128-thread CTAs were the fastest family in the 512^3 launch-shape sweep (profiles/r01_sweep.md)
     const int quads = static_cast<int>(h->nx / 4);
     int bx = h->tune.bx, by = h->tune.by;
     if (bx == 0) bx = quads >= 128 ? 128 : (quads > 32 ? 64 : 32);
-    if (by == 0) by = 256 / bx;
+    if (by == 0) by = 128 / bx;
     for (int s = 0; s < kNumShapes; ++s)
         if (kShapes[s].bx == bx && kShapes[s].by == by) return s;
-    return bx >= 128 ? 5 : (bx == 64 ? 3 : 1);
+    return bx >= 128 ? 2 : (bx == 64 ? 1 : 0);
 }
 
 int pick_zc(fdtd_b200_handle h, int planes) {
@@ -224,12 +221,12 @@ int pick_zc(fdtd_b200_handle h, int planes) {
     // z∓1 prologue plane (2 of 9 streams) stays a small fraction of the traffic
     const Shape sh = kShapes[pick_shape(h)];
     const long long row_blocks = ((static_cast<long long>(h->nx) / 4 + sh.bx - 1) / sh.bx) * ((static_cast<long long>(h->ny) + sh.by - 1) / sh.by);
-    int zc = 32;
+    int zc = 16;
     while (zc > 4 && row_blocks * ((planes + zc - 1) / zc) < 148LL * 16) zc >>= 1;
     return zc;
 }
 
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 int launch_h_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     const LatticeView L = lattice_view(h);
     const ForcingView F = forcing_view(h);
@@ -251,7 +248,7 @@ int launch_h_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     return FDTD_B200_OK;
 }
 
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 int launch_e_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     const LatticeView L = lattice_view(h);
     const ForcingView F = forcing_view(h);
@@ -274,6 +271,17 @@ int launch_e_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     return FDTD_B200_OK;
 }
 
+// 0 fast | 1 exact with exact reciprocals (every dx, cast to f32, is a power of two) | 2 exact with IEEE division
+int arithmetic_mode(fdtd_b200_handle h) {
+    if (!(h->flags & FDTD_B200_EXACT_ARITHMETIC)) return 0;
+    for (int a = 0; a < 3; ++a) {
+        int e = 0;
+        const float m = std::frexp(static_cast<float>(h->cfg.dx[a]), &e);
+        if (m != 0.5f || e < -100 || e > 100) return 2;
+    }
+    return 1;
+}
+
 int prof_begin(fdtd_b200_handle h, int which, int planes) {
     if (!h->profiling) return FDTD_B200_OK;
     cudaEvent_t a, b;
@@ -292,21 +300,21 @@ int prof_end(fdtd_b200_handle h, int which) {
 
 int launch_h(fdtd_b200_handle h, int z_lo, int z_hi) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
-    const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
+    const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = exact ? launch_h_t<true, uint8_t>(h, z_lo, z_hi) : launch_h_t<false, uint8_t>(h, z_lo, z_hi);
-    else rc = exact ? launch_h_t<true, uint16_t>(h, z_lo, z_hi) : launch_h_t<false, uint16_t>(h, z_lo, z_hi);
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_h_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint8_t>(h, z_lo, z_hi) : launch_h_t<2, uint8_t>(h, z_lo, z_hi));
+    else rc = mode == 0 ? launch_h_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint16_t>(h, z_lo, z_hi) : launch_h_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
     return prof_end(h, 0);
 }
 int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
-    const bool exact = (h->flags & FDTD_B200_EXACT_ARITHMETIC) != 0;
+    const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 1, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = exact ? launch_e_t<true, uint8_t>(h, z_lo, z_hi) : launch_e_t<false, uint8_t>(h, z_lo, z_hi);
-    else rc = exact ? launch_e_t<true, uint16_t>(h, z_lo, z_hi) : launch_e_t<false, uint16_t>(h, z_lo, z_hi);
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_e_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint8_t>(h, z_lo, z_hi) : launch_e_t<2, uint8_t>(h, z_lo, z_hi));
+    else rc = mode == 0 ? launch_e_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint16_t>(h, z_lo, z_hi) : launch_e_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
     return prof_end(h, 1);
 }

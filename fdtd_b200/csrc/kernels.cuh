@@ -51,15 +51,20 @@ __device__ __forceinline__ int lower_bound_ll(const long long* __restrict__ a, i
     return lo;
 }
 
-// (f_hi - f_lo) / dx.  EXACT: IEEE division as update.wgsl:159,171; otherwise reciprocal multiply.
-template <bool EXACT>
+// Arithmetic modes (template parameter EXACT):
+//   0  fast:  (hi - lo) * (1/dx), FMA contraction allowed;
+//   1  exact, every dx a power of two: x * (1/dx) is bit-identical to x / dx, so multiply, no contraction;
+//   2  exact, general dx: IEEE division as update.wgsl:159,171.
+// (f_hi - f_lo) / dx:
+template <int EXACT>
 __device__ __forceinline__ float deriv(float hi, float lo, float dx, float inv_dx) {
-    if (EXACT) return __fdiv_rn(__fsub_rn(hi, lo), dx);
+    if (EXACT == 2) return __fdiv_rn(__fsub_rn(hi, lo), dx);
+    if (EXACT == 1) return __fmul_rn(__fsub_rn(hi, lo), inv_dx);
     return (hi - lo) * inv_dx;
 }
 
 // a*prev + b*(c - s + psi), psi = 0 (update.wgsl:89,127; cpu/mod.rs:460-461, 502-503).
-template <bool EXACT>
+template <int EXACT>
 __device__ __forceinline__ float leap(float a, float prev, float b, float c, float s) {
     if (EXACT) {
         float t = __fsub_rn(c, s);
@@ -104,7 +109,7 @@ __device__ __forceinline__ float pick(const float4& v, int k) { return k == 0 ? 
 // ------------------------------------------------------------------------------------------------
 
 // H' = d_a·H + d_b·(−∇×E − M); backward differences, zero where x_i == 0 (update.wgsl:56-91, 155-165).
-template <bool EXACT, typename IdxT, int BX, int BY>
+template <int EXACT, typename IdxT, int BX, int BY>
 __global__ void __launch_bounds__(BX * BY)
 k_update_h_vec4(const LatticeView L, const ForcingView F, const int z_lo, const int z_hi, const int zc) {
     extern __shared__ float2 s_tab[];
@@ -196,7 +201,7 @@ k_update_h_vec4(const LatticeView L, const ForcingView F, const int z_lo, const 
 
 // E' = c_a·E + c_b·(∇×H' − J); forward differences on the new H, zero where x_i + 1 == n_i
 // (update.wgsl:94-129, 167-177).  Probe sampling of (E', H') is fused here.
-template <bool EXACT, typename IdxT, int BX, int BY>
+template <int EXACT, typename IdxT, int BX, int BY>
 __global__ void __launch_bounds__(BX * BY)
 k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, const int z_lo, const int z_hi, const int zc) {
     extern __shared__ float2 s_tab[];
@@ -307,7 +312,7 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
 template <typename IdxT>
 __device__ __forceinline__ int mat_at(const void* base, size_t i) { return static_cast<const IdxT*>(base)[i]; }
 
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 __global__ void __launch_bounds__(256)
 k_update_h_generic(const LatticeView L, const ForcingView F, const int z_lo, const int z_hi) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -342,7 +347,7 @@ k_update_h_generic(const LatticeView L, const ForcingView F, const int z_lo, con
     }
 }
 
-template <bool EXACT, typename IdxT>
+template <int EXACT, typename IdxT>
 __global__ void __launch_bounds__(256)
 k_update_e_generic(const LatticeView L, const ForcingView F, const ProbeView P, const int z_lo, const int z_hi) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;

@@ -66,6 +66,20 @@ def test_exact_mode_is_bit_identical_to_f32_oracle(b200, oracle, size, generic):
     assert np.array_equal(h, ref.field(oracle.H).astype(np.float32))
 
 
+@pytest.mark.parametrize("size", [(32, 10, 9), (10, 9, 8)])
+def test_exact_mode_with_true_division(b200, oracle, size):
+    """dx not a power of two → the kernels divide (update.wgsl:159,171) instead of multiplying by 1/dx."""
+    w = _random_workload(b200, size, seed=21, dx=(0.3, 0.7, 1.1), dt=0.11)
+    init = random_fields(w, seed=6)
+    ref, _ = oracle_run(oracle, w, 15, oracle.F32, init=init)
+    _, st, _ = b200_run(b200, w, 15, exact=True, init=init)
+    e, h = _fields(st, b200)
+    assert np.array_equal(e, ref.field(oracle.E).astype(np.float32)) and np.array_equal(h, ref.field(oracle.H).astype(np.float32))
+    _, stf, _ = b200_run(b200, w, 15, exact=False, init=init)
+    ef, hf = _fields(stf, b200)
+    assert rel_l2(ef, ref.field(oracle.E)) <= TOL_FAST_VS_F32 and rel_l2(hf, ref.field(oracle.H)) <= TOL_FAST_VS_F32
+
+
 @pytest.mark.parametrize("size", [(64, 24, 20), (36, 9, 11), (9, 10, 11)])
 def test_fast_mode_within_tolerance(b200, oracle, size):
     w = _random_workload(b200, size, seed=5)
