@@ -62,6 +62,7 @@ SYMBOLS = {
     "fdtd_b200_last_error": (C.c_char_p, [_H]),
     "fdtd_b200_reset": (C.c_int, [_H]),
     "fdtd_b200_set_stream": (C.c_int, [_H, C.c_void_p]),
+    "fdtd_b200_reset_stream": (C.c_int, [_H]),
     "fdtd_b200_sync": (C.c_int, [_H]),
     "fdtd_b200_tick": (C.c_uint64, [_H]),
     "fdtd_b200_time": (C.c_double, [_H]),

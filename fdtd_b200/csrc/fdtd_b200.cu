@@ -611,7 +611,15 @@ int fdtd_b200_set_stream(fdtd_b200_handle h, void* cuda_stream) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
     if (int rc = set_device(h)) return rc;
     CU_TRY(h, cudaStreamSynchronize(h->stream));
-    h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
+    h->stream = static_cast<cudaStream_t>(cuda_stream);  // NULL is a valid stream: the legacy default stream
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_reset_stream(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    h->stream = h->own_stream;
     return FDTD_B200_OK;
 }
 

@@ -344,8 +344,12 @@ class FdtdB200SolverState:
     def reset(self) -> None:
         L.check(self._lib.fdtd_b200_reset(self._h), self._h)
 
-    def set_stream(self, cuda_stream: Optional[int]) -> None:
-        L.check(self._lib.fdtd_b200_set_stream(self._h, C.c_void_p(cuda_stream or 0)), self._h)
+    def set_stream(self, cuda_stream: int) -> None:
+        """Run on this cudaStream_t (0 = the legacy default stream = torch's default stream)."""
+        L.check(self._lib.fdtd_b200_set_stream(self._h, C.c_void_p(int(cuda_stream))), self._h)
+
+    def reset_stream(self) -> None:
+        L.check(self._lib.fdtd_b200_reset_stream(self._h), self._h)
 
     def register_probes(self, points: Sequence[Point]) -> None:
         cells = np.array([self.cell_index(p) for p in points], dtype=np.uint64)

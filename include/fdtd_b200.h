@@ -150,8 +150,10 @@ const char* fdtd_b200_last_error(fdtd_b200_handle h);
 
 /* A fresh `create_state` (cpu/mod.rs:310-322): zero fields, clear sources, tick = 0, time = 0. */
 int fdtd_b200_reset(fdtd_b200_handle h);
-/* Run subsequent work on this CUDA stream (a cudaStream_t; NULL restores the handle's own). */
+/* Run subsequent work on this CUDA stream (a cudaStream_t; NULL means the legacy default stream, which is
+ * what torch's default stream is).  reset_stream goes back to the handle's own non-blocking stream. */
 int fdtd_b200_set_stream(fdtd_b200_handle h, void* cuda_stream);
+int fdtd_b200_reset_stream(fdtd_b200_handle h);
 int fdtd_b200_sync(fdtd_b200_handle h);
 
 /* `Time` (lib.rs:92-95).  time is accumulated `time += dt` in f64 (cpu/mod.rs:513). */
