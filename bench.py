@@ -289,8 +289,18 @@ def run_b200(args) -> None:
             kern.append({"kernel": name, "avg_ms": tot_ms / n_l, "launches": int(n_l),
                          "achieved": BYTES_PER_CELL_HALF_STEP * n_cells / (tot_ms * 1e-3) / 1e9})
     dom = min(kern, key=lambda k: k["achieved"])
+    traffic = None
+    try:  # per-launch DRAM bytes of the dominant kernel from the committed ncu capture (same lattice only)
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tr = json.load(f)
+        if n_gpus == 1 and list(lattice) == tr["lattice"]:
+            key = ("k_update_h" if dom["kernel"] == "update_h" else "k_update_e") + ("_bulk" if st.uses_bulk else "_vec4")
+            traffic = tr[key]["dram_read_bytes"] + tr[key]["dram_write_bytes"]
+    except Exception:
+        traffic = None
     roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["achieved"] / peak,
-                "traffic": None, "kernel": dom["kernel"], "kernel_avg_ms": dom["avg_ms"], "peak_source": peak_src,
+                "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+                "algorithmic_bytes_per_launch": BYTES_PER_CELL_HALF_STEP * cells_total / n_gpus, "kernel": dom["kernel"], "kernel_avg_ms": dom["avg_ms"], "peak_source": peak_src,
                 "algorithmic_bytes_per_cell_half_step": BYTES_PER_CELL_HALF_STEP,
                 "step_achieved_gbs": BYTES_PER_CELL_STEP * value * (1.0 / n_gpus), "step_frac": BYTES_PER_CELL_STEP * value / n_gpus / peak,
                 "kernels": kern}

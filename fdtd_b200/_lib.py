@@ -68,6 +68,7 @@ SYMBOLS = {
     "fdtd_b200_time": (C.c_double, [_H]),
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
+    "fdtd_b200_uses_bulk": (C.c_int, [_H]),
     "fdtd_b200_kernel_launches": (C.c_uint64, [_H]),
     "fdtd_b200_set_profiling": (C.c_int, [_H, C.c_int]),
     "fdtd_b200_get_profile": (C.c_int, [_H, C.c_int, C.POINTER(C.c_double), _u64p, _u64p]),

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "kernels_bulk.cuh"
 
 using namespace fdtd_b200;
 
@@ -23,6 +24,8 @@ thread_local std::string g_error;
 
 struct Tune {
     int bx = 0, by = 0, zc = 0;  // 0 = choose automatically
+    int variant = -1;            // -1 auto | 0 register-streaming kernels | 1 TMA bulk-copy staged kernels
+    int stages = 0;              // ring depth of the staged kernels (0 = default)
 };
 
 }  // namespace
@@ -124,8 +127,8 @@ bool c_or_d(double perm, double sigma, double dt, double* a, double* b) {
 Tune parse_tune() {
     Tune t;
     if (const char* s = std::getenv("FDTD_B200_TUNE")) {
-        int a = 0, b = 0, c = 0;
-        if (std::sscanf(s, "%d,%d,%d", &a, &b, &c) >= 1) { t.bx = a; t.by = b; t.zc = c; }
+        int a = 0, b = 0, c = 0, d = -1, e = 0;
+        if (std::sscanf(s, "%d,%d,%d,%d,%d", &a, &b, &c, &d, &e) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; }
     }
     return t;
 }
@@ -271,6 +274,84 @@ int launch_e_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     return FDTD_B200_OK;
 }
 
+
+// ---- TMA bulk-copy staged kernels (kernels_bulk.cuh) ------------------------------------------------
+struct BulkShape { int bx, by, s; };
+constexpr BulkShape kBulkShapes[] = {{128, 1, 4}, {128, 2, 3}, {128, 2, 4}, {128, 4, 2}, {128, 4, 3}, {32, 4, 4}};
+constexpr int kNumBulkShapes = sizeof(kBulkShapes) / sizeof(kBulkShapes[0]);
+
+bool bulk_eligible(fdtd_b200_handle h) {
+    // bulk copies need 16-byte aligned rows of every stream, including the 1- or 2-byte material index
+    return h->vec4 && (h->nx * h->idx_bytes) % 16 == 0;
+}
+
+int pick_bulk_shape(fdtd_b200_handle h) {
+    int bx = h->tune.bx, by = h->tune.by, st = h->tune.stages;
+    if (bx == 0) bx = h->nx >= 512 ? 128 : 32;
+    if (bx != 128) { bx = 32; }
+    if (by == 0) by = bx == 128 ? 2 : 4;
+    if (st == 0) st = bx == 128 ? (by == 1 ? 4 : 3) : 4;
+    for (int s = 0; s < kNumBulkShapes; ++s)
+        if (kBulkShapes[s].bx == bx && kBulkShapes[s].by == by && kBulkShapes[s].s == st) return s;
+    return bx == 128 ? 1 : 5;
+}
+
+template <int EXACT, typename IdxT, int BX, int BY, int S>
+int launch_bulk(fdtd_b200_handle h, bool e_step, int z_lo, int z_hi) {
+    const LatticeView L = lattice_view(h);
+    const ForcingView F = forcing_view(h);
+    int zc = h->tune.zc;
+    if (zc <= 0) {
+        // long marches amortise the ring's fill latency; keep >= ~3 waves of CTAs over the 148 SMs
+        const long long tiles = static_cast<long long>((L.nx + 4 * BX - 1) / (4 * BX)) * ((L.ny + BY - 1) / BY);
+        zc = 64;
+        while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
+    }
+    dim3 block(BX, BY, 1);
+    dim3 grid((L.nx + 4 * BX - 1) / (4 * BX), (L.ny + BY - 1) / BY, (z_hi - z_lo + zc - 1) / zc);
+    const size_t smem = bulk_smem_bytes<BX, BY, S, IdxT>(L.table_in_smem ? L.n_table : 0);
+    if (e_step) {
+        const ProbeView P = probe_view(h);
+        auto k = k_update_e_bulk<EXACT, IdxT, BX, BY, S>;
+        CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        k<<<grid, block, smem, h->stream>>>(L, F, P, z_lo, z_hi, zc);
+    } else {
+        auto k = k_update_h_bulk<EXACT, IdxT, BX, BY, S>;
+        CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        k<<<grid, block, smem, h->stream>>>(L, F, z_lo, z_hi, zc);
+    }
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+template <int EXACT, typename IdxT>
+int launch_bulk_shape(fdtd_b200_handle h, bool e_step, int z_lo, int z_hi) {
+    switch (pick_bulk_shape(h)) {
+        case 0: return launch_bulk<EXACT, IdxT, 128, 1, 4>(h, e_step, z_lo, z_hi);
+        case 1: return launch_bulk<EXACT, IdxT, 128, 2, 3>(h, e_step, z_lo, z_hi);
+        case 2: return launch_bulk<EXACT, IdxT, 128, 2, 4>(h, e_step, z_lo, z_hi);
+        case 3: return launch_bulk<EXACT, IdxT, 128, 4, 2>(h, e_step, z_lo, z_hi);
+        case 4: return launch_bulk<EXACT, IdxT, 128, 4, 3>(h, e_step, z_lo, z_hi);
+        default: return launch_bulk<EXACT, IdxT, 32, 4, 4>(h, e_step, z_lo, z_hi);
+    }
+}
+
+int launch_bulk_any(fdtd_b200_handle h, bool e_step, int z_lo, int z_hi, int mode) {
+    if (h->idx_bytes == 1) {
+        return mode == 0 ? launch_bulk_shape<0, uint8_t>(h, e_step, z_lo, z_hi)
+                         : (mode == 1 ? launch_bulk_shape<1, uint8_t>(h, e_step, z_lo, z_hi) : launch_bulk_shape<2, uint8_t>(h, e_step, z_lo, z_hi));
+    }
+    return mode == 0 ? launch_bulk_shape<0, uint16_t>(h, e_step, z_lo, z_hi)
+                     : (mode == 1 ? launch_bulk_shape<1, uint16_t>(h, e_step, z_lo, z_hi) : launch_bulk_shape<2, uint16_t>(h, e_step, z_lo, z_hi));
+}
+
+bool use_bulk(fdtd_b200_handle h) {
+    if (!bulk_eligible(h) || h->tune.variant == 0) return false;
+    if (h->tune.variant == 1) return true;
+    return h->nx >= 128;  // auto: the staged kernels win on wide rows (profiles/r01_sweep_bulk.jsonl)
+}
+
 // 0 fast | 1 exact with exact reciprocals (every dx, cast to f32, is a power of two) | 2 exact with IEEE division
 int arithmetic_mode(fdtd_b200_handle h) {
     if (!(h->flags & FDTD_B200_EXACT_ARITHMETIC)) return 0;
@@ -303,7 +384,8 @@ int launch_h(fdtd_b200_handle h, int z_lo, int z_hi) {
     const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = mode == 0 ? launch_h_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint8_t>(h, z_lo, z_hi) : launch_h_t<2, uint8_t>(h, z_lo, z_hi));
+    if (use_bulk(h)) rc = launch_bulk_any(h, false, z_lo, z_hi, mode);
+    else if (h->idx_bytes == 1) rc = mode == 0 ? launch_h_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint8_t>(h, z_lo, z_hi) : launch_h_t<2, uint8_t>(h, z_lo, z_hi));
     else rc = mode == 0 ? launch_h_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint16_t>(h, z_lo, z_hi) : launch_h_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
     return prof_end(h, 0);
@@ -313,7 +395,8 @@ int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
     const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 1, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = mode == 0 ? launch_e_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint8_t>(h, z_lo, z_hi) : launch_e_t<2, uint8_t>(h, z_lo, z_hi));
+    if (use_bulk(h)) rc = launch_bulk_any(h, true, z_lo, z_hi, mode);
+    else if (h->idx_bytes == 1) rc = mode == 0 ? launch_e_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint8_t>(h, z_lo, z_hi) : launch_e_t<2, uint8_t>(h, z_lo, z_hi));
     else rc = mode == 0 ? launch_e_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint16_t>(h, z_lo, z_hi) : launch_e_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
     return prof_end(h, 1);
@@ -634,6 +717,7 @@ uint64_t fdtd_b200_tick(fdtd_b200_handle h) { return h ? h->tick : 0; }
 double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
 int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }
 int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
+int fdtd_b200_uses_bulk(fdtd_b200_handle h) { return h && use_bulk(h) ? 1 : 0; }
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h) { return h ? h->launches : 0; }
 
 int fdtd_b200_set_profiling(fdtd_b200_handle h, int enabled) {

@@ -101,6 +101,22 @@ __device__ __noinline__ float3 forcing_lookup(const ForcingView F, int s0, int c
     return v;
 }
 
+// Does any of the (sorted) cells lie inside the CTA's box [x0,x1) x [y0,y1) x [z0,z1)?  Evaluated once per CTA so
+// that the per-plane forcing / probe lookups cost nothing in the (vast majority of) CTAs that own none.
+__device__ __forceinline__ bool any_cell_in_box(const long long* __restrict__ cells, int n, int tid, int nthreads, int x0, int x1,
+                                                int y0, int y1, int z0, int z1, int nx, long long sz) {
+    bool hit = false;
+    for (int s = tid; s < n; s += nthreads) {
+        const long long c = __ldg(cells + s);
+        const int z = static_cast<int>(c / sz);
+        const long long r = c - static_cast<long long>(z) * sz;
+        const int yy = static_cast<int>(r / nx);
+        const int xx = static_cast<int>(r - static_cast<long long>(yy) * nx);
+        hit |= (z >= z0) && (z < z1) && (yy >= y0) && (yy < y1) && (xx >= x0) && (xx < x1);
+    }
+    return hit;
+}
+
 __device__ __forceinline__ float pick(const float4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
 
 // ------------------------------------------------------------------------------------------------
@@ -120,14 +136,18 @@ k_update_h_vec4(const LatticeView L, const ForcingView F, const int z_lo, const 
         }
     }
     __syncthreads();
+    const int za = z_lo + blockIdx.z * zc;
+    const int zb = min(za + zc, z_hi);
+    const long long sz_ll = static_cast<long long>(L.nx) * L.ny;
+    bool has_src = false;
+    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, threadIdx.y * BX + threadIdx.x, BX * BY, blockIdx.x * BX * 4,
+                                                        (blockIdx.x + 1) * BX * 4, blockIdx.y * BY, (blockIdx.y + 1) * BY, za, zb, L.nx, sz_ll)) != 0;
 
     const int y = blockIdx.y * BY + threadIdx.y;
     if (y >= L.ny) return;
     const int x_raw = (blockIdx.x * BX + threadIdx.x) * 4;
     const bool act = x_raw < L.nx;
     const int x = act ? x_raw : L.nx - 4;  // surplus lanes shadow the last quad and never store
-    const int za = z_lo + blockIdx.z * zc;
-    const int zb = min(za + zc, z_hi);
     if (za >= zb) return;
     const unsigned lane = threadIdx.x & 31u;
     const size_t sy = static_cast<size_t>(L.nx);
@@ -152,7 +172,7 @@ k_update_h_vec4(const LatticeView L, const ForcingView F, const int z_lo, const 
         if (lane == 0 && x_in) { ey_l = L.ey[i - 1]; ez_l = L.ez[i - 1]; }
 
         int s0 = 0, cnt = 0;
-        if (F.n) {
+        if (has_src) {
             s0 = lower_bound_ll(F.cells, F.n, static_cast<long long>(i));
             while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < static_cast<long long>(i) + 4) ++cnt;
         }
@@ -212,14 +232,20 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
         }
     }
     __syncthreads();
+    const int za = z_lo + blockIdx.z * zc;
+    const int zb = min(za + zc, z_hi);
+    const long long sz_ll = static_cast<long long>(L.nx) * L.ny;
+    bool has_src = false, has_probe = false;
+    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, threadIdx.y * BX + threadIdx.x, BX * BY, blockIdx.x * BX * 4,
+                                                        (blockIdx.x + 1) * BX * 4, blockIdx.y * BY, (blockIdx.y + 1) * BY, za, zb, L.nx, sz_ll)) != 0;
+    if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, threadIdx.y * BX + threadIdx.x, BX * BY, blockIdx.x * BX * 4,
+                                                          (blockIdx.x + 1) * BX * 4, blockIdx.y * BY, (blockIdx.y + 1) * BY, za, zb, L.nx, sz_ll)) != 0;
 
     const int y = blockIdx.y * BY + threadIdx.y;
     if (y >= L.ny) return;
     const int x_raw = (blockIdx.x * BX + threadIdx.x) * 4;
     const bool act = x_raw < L.nx;
     const int x = act ? x_raw : L.nx - 4;
-    const int za = z_lo + blockIdx.z * zc;
-    const int zb = min(za + zc, z_hi);
     if (za >= zb) return;
     const unsigned lane = threadIdx.x & 31u;
     const size_t sy = static_cast<size_t>(L.nx);
@@ -245,7 +271,7 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
         if (lane == 31 && x_in) { hz_r = L.hz[i + 4]; hy_r = L.hy[i + 4]; }
 
         int s0 = 0, cnt = 0;
-        if (F.n) {
+        if (has_src) {
             s0 = lower_bound_ll(F.cells, F.n, static_cast<long long>(i));
             while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < static_cast<long long>(i) + 4) ++cnt;
         }
@@ -290,7 +316,7 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
             st4(L.ex + i, ex);
             st4(L.ey + i, ey);
             st4(L.ez + i, ez);
-            if (P.n) {
+            if (has_probe) {
                 for (int s = lower_bound_ll(P.cells, P.n, static_cast<long long>(i)); s < P.n; ++s) {
                     const long long c = __ldg(P.cells + s);
                     if (c >= static_cast<long long>(i) + 4) break;

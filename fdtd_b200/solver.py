@@ -436,6 +436,10 @@ class FdtdB200SolverState:
         return bool(self._lib.fdtd_b200_uses_vec4(self._h))
 
     @property
+    def uses_bulk(self) -> bool:
+        return bool(self._lib.fdtd_b200_uses_bulk(self._h))
+
+    @property
     def kernel_launches(self) -> int:
         return int(self._lib.fdtd_b200_kernel_launches(self._h))
 

@@ -163,6 +163,7 @@ double fdtd_b200_time(fdtd_b200_handle h);
 /* Introspection used by tests and the bench. */
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
 int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */
+int fdtd_b200_uses_bulk(fdtd_b200_handle h);     /* 1 when the TMA bulk-copy staged kernels run */
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h); /* kernels launched so far by this handle */
 /* Measurement: with profiling on, every H / E half-step launch is bracketed by CUDA events on the
  * handle's stream.  get_profile(which = 0 H | 1 E) blocks and returns the summed device time, the
