@@ -11,6 +11,7 @@ OK, EINVAL, ENOMEM, ECUDA, ESTATE = 0, 1, 2, 3, 4
 FIELD_E, FIELD_H = 0, 1
 EXACT_ARITHMETIC = 1 << 0
 FORCE_GENERIC_KERNELS = 1 << 1
+FUSED_STEP = 1 << 2
 COLORMAP_CPU, COLORMAP_LINEAR, COLORMAP_APP_Z = 0, 1, 2
 (HALO_SEND_EX_TOP, HALO_SEND_EY_TOP, HALO_RECV_EX_LOW, HALO_RECV_EY_LOW,
  HALO_SEND_HX_BOTTOM, HALO_SEND_HY_BOTTOM, HALO_RECV_HX_HIGH, HALO_RECV_HY_HIGH) = range(8)
@@ -69,6 +70,7 @@ SYMBOLS = {
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
     "fdtd_b200_uses_bulk": (C.c_int, [_H]),
+    "fdtd_b200_uses_fused": (C.c_int, [_H]),
     "fdtd_b200_kernel_launches": (C.c_uint64, [_H]),
     "fdtd_b200_set_profiling": (C.c_int, [_H, C.c_int]),
     "fdtd_b200_get_profile": (C.c_int, [_H, C.c_int, C.POINTER(C.c_double), _u64p, _u64p]),

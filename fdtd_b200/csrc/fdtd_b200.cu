@@ -15,6 +15,7 @@
 
 #include "kernels.cuh"
 #include "kernels_bulk.cuh"
+#include "kernels_fused.cuh"
 
 using namespace fdtd_b200;
 
@@ -44,6 +45,9 @@ struct fdtd_b200_solver {
 
     float* alloc[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // ghost + planes + ghost
     float* f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};      // plane 0
+    float* alt_alloc[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // ping-pong set of the fused step
+    float* g[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool fused = false;
     void* mat = nullptr;
     int idx_bytes = 1;
     float4* table = nullptr;
@@ -352,6 +356,42 @@ bool use_bulk(fdtd_b200_handle h) {
     return h->nx >= 128;  // auto: the staged kernels win on wide rows (profiles/r01_sweep_bulk.jsonl)
 }
 
+
+// ---- fused single-pass step (kernels_fused.cuh) --------------------------------------------------------
+bool fused_eligible(const fdtd_b200_config& cfg, uint64_t nzl, int idx_bytes, bool vec4) {
+    const bool whole = (cfg.z_begin == 0) && (cfg.z_end == 0 || cfg.z_end == cfg.nz) && nzl == cfg.nz;
+    return whole && vec4 && (cfg.nx * idx_bytes) % 16 == 0 && cfg.nx >= 128;
+}
+
+template <int EXACT, typename IdxT>
+int launch_fused_t(fdtd_b200_handle h) {
+    constexpr int BX = 32, BY = 8;
+    using LO = FusedLayout<IdxT, BX, BY>;
+    FusedView V{};
+    for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
+    V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table);
+    V.table_in_smem = h->n_table <= 64 ? 1 : 0;
+    V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
+    for (int a = 0; a < 3; ++a) { V.dx[a] = static_cast<float>(h->cfg.dx[a]); V.inv_dx[a] = 1.0f / V.dx[a]; }
+    const ForcingView F = forcing_view(h);
+    const ProbeView P = probe_view(h);
+    int zc = h->tune.zc;
+    if (zc <= 0) {
+        const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + BY - 1) / BY);
+        zc = 64;
+        while (zc > 8 && tiles * ((V.nz + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
+    }
+    dim3 block(BX, BY, 1);
+    dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + BY - 1) / BY, (V.nz + zc - 1) / zc);
+    const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0);
+    auto k = k_step_fused<EXACT, IdxT, BX, BY>;
+    CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    k<<<grid, block, smem, h->stream>>>(V, F, P, zc);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
 // 0 fast | 1 exact with exact reciprocals (every dx, cast to f32, is a power of two) | 2 exact with IEEE division
 int arithmetic_mode(fdtd_b200_handle h) {
     if (!(h->flags & FDTD_B200_EXACT_ARITHMETIC)) return 0;
@@ -408,6 +448,18 @@ void prof_clear(fdtd_b200_handle h) {
         h->prof_events[w].clear();
         h->prof_cells[w] = 0;
     }
+}
+
+int launch_fused(fdtd_b200_handle h) {
+    const int mode = arithmetic_mode(h);
+    if (int rc = prof_begin(h, 0, static_cast<int>(h->nzl))) return rc;
+    int rc;
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h) : (mode == 1 ? launch_fused_t<1, uint8_t>(h) : launch_fused_t<2, uint8_t>(h));
+    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h) : (mode == 1 ? launch_fused_t<1, uint16_t>(h) : launch_fused_t<2, uint16_t>(h));
+    if (rc) return rc;
+    if (int rc2 = prof_end(h, 0)) return rc2;
+    for (int c = 0; c < 6; ++c) { std::swap(h->f[c], h->g[c]); std::swap(h->alloc[c], h->alt_alloc[c]); }
+    return FDTD_B200_OK;
 }
 
 void end_step(fdtd_b200_handle h) {
@@ -491,6 +543,15 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
         CU_NEW(cudaMalloc(&h->alloc[c], comp_floats * sizeof(float)));
         CU_NEW(cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
         h->f[c] = h->alloc[c] + h->plane;
+    }
+    h->fused = ((cfg->flags & FDTD_B200_FUSED_STEP) || h->tune.variant == 2) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
+               fused_eligible(h->cfg, h->nzl, h->idx_bytes, h->vec4);
+    if (h->fused) {
+        for (int c = 0; c < 6; ++c) {
+            CU_NEW(cudaMalloc(&h->alt_alloc[c], comp_floats * sizeof(float)));
+            CU_NEW(cudaMemsetAsync(h->alt_alloc[c], 0, comp_floats * sizeof(float), h->stream));
+            h->g[c] = h->alt_alloc[c] + h->plane;
+        }
     }
     // material index (+8 bytes slack so the last quad's vector load never leaves the allocation)
     CU_NEW(cudaMalloc(&h->mat, h->n_local * h->idx_bytes + 16));
@@ -628,7 +689,9 @@ size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_byt
     const uint64_t plane = cfg->nx * cfg->ny;
     // 6 fp32 components with two ghost planes each + the material index (cf. 136 B/cell cpu/mod.rs:217-221,
     // 80 B/cell wgpu/mod.rs:129-133)
-    return static_cast<size_t>(6 * sizeof(float) * plane * (nzl + 2) + plane * nzl * index_bytes + 16);
+    const bool fused = (cfg->flags & FDTD_B200_FUSED_STEP) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
+                       fused_eligible(*cfg, nzl, static_cast<int>(index_bytes), cfg->nx % 4 == 0);
+    return static_cast<size_t>((fused ? 12 : 6) * sizeof(float) * plane * (nzl + 2) + plane * nzl * index_bytes + 16);
 }
 
 int fdtd_b200_create_from_table(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
@@ -658,6 +721,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
     for (int c = 0; c < 6; ++c) if (h->alloc[c]) cudaFree(h->alloc[c]);
+    for (int c = 0; c < 6; ++c) if (h->alt_alloc[c]) cudaFree(h->alt_alloc[c]);
     if (h->mat) cudaFree(h->mat);
     if (h->table) cudaFree(h->table);
     if (h->d_src_cells) cudaFree(h->d_src_cells);
@@ -681,6 +745,8 @@ int fdtd_b200_reset(fdtd_b200_handle h) {
     if (int rc = set_device(h)) return rc;
     const size_t comp_floats = static_cast<size_t>(h->plane) * (h->nzl + 2);
     for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
+    if (h->fused)
+        for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alt_alloc[c], 0, comp_floats * sizeof(float), h->stream));
     if (h->d_probe_ring)
         CU_TRY(h, cudaMemsetAsync(h->d_probe_ring, 0, sizeof(float) * 6 * h->n_probes_total * static_cast<size_t>(h->ring_steps), h->stream));
     h->n_src = 0; h->src_rows = 0; h->src_row = 0;
@@ -718,6 +784,7 @@ double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
 int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }
 int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
 int fdtd_b200_uses_bulk(fdtd_b200_handle h) { return h && use_bulk(h) ? 1 : 0; }
+int fdtd_b200_uses_fused(fdtd_b200_handle h) { return h && h->fused ? 1 : 0; }
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h) { return h ? h->launches : 0; }
 
 int fdtd_b200_set_profiling(fdtd_b200_handle h, int enabled) {
@@ -889,8 +956,12 @@ int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
     if (int rc = set_device(h)) return rc;
     const int nzl = static_cast<int>(h->nzl);
     for (uint64_t s = 0; s < n_steps; ++s) {
-        if (int rc = launch_h(h, 0, nzl)) return rc;
-        if (int rc = launch_e(h, 0, nzl)) return rc;
+        if (h->fused) {
+            if (int rc = launch_fused(h)) return rc;
+        } else {
+            if (int rc = launch_h(h, 0, nzl)) return rc;
+            if (int rc = launch_e(h, 0, nzl)) return rc;
+        }
         end_step(h);
     }
     return FDTD_B200_OK;

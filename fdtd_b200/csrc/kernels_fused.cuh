@@ -1,0 +1,327 @@
+// Fused leapfrog step (north_star item 4, "temporal blocking" of the two half-steps): ONE pass over the lattice
+// computes H' = d_a·H + d_b·(−∇×E − M) and E' = c_a·E + c_b·(∇×H' − J) (cem-solver/src/fdtd/cpu/mod.rs:416-515,
+// fdtd/wgpu/update.wgsl:56-177), so a cell update moves 6 fp32 reads + 6 fp32 writes + 1 B index = 49 B instead of 74 B.
+//
+// E'(p) needs H' at p, p+x, p+y, p+z, and a neighbouring CTA cannot see this CTA's fresh H' in time, so every CTA
+// recomputes H' on its tile extended by one column, one row and one plane (overlapped tiling).  That recomputation reads
+// the OLD fields of cells another CTA is updating, hence the step is out of place: fields are ping-pong buffered
+// (in → out) and the handle swaps the two sets after the launch.
+//
+// Data movement: old E (3 planes resident: z-1, z, z+1 in flight) and old H + material index (2 planes) are streamed
+// into shared-memory rings by 1-D TMA bulk copies (UBLKCP) completing on mbarriers; the fresh H' of two consecutive
+// planes is exchanged between threads through a double-buffered shared-memory tile.  One __syncthreads per plane.
+// Arithmetic = the helpers of kernels.cuh → bit-identical to the two-kernel path.
+#pragma once
+
+#include "kernels_bulk.cuh"
+
+namespace fdtd_b200 {
+
+struct FusedView {
+    const float* in[6];   // Ex Ey Ez Hx Hy Hz of the current step (plane 0)
+    float* out[6];        // the other buffer set
+    const void* mat;
+    const float4* table;
+    int n_table, table_in_smem;
+    int nx, ny, nz;
+    float dx[3], inv_dx[3];
+};
+
+template <typename IdxT, int BX, int BY>
+struct FusedLayout {
+    static constexpr int NT = BX * BY;
+    static constexpr int PE = 4 * BX + 8;                       // field row pitch: [left halo quad][4*BX cells][right halo quad]
+    static constexpr int ME = 16 / static_cast<int>(sizeof(IdxT));  // extra index entries fetched to the right (16 bytes)
+    static constexpr int PM = 4 * BX + ME;                      // index row pitch (entries)
+    static constexpr int E_ROWS = BY + 2, H_ROWS = BY + 1;
+    static constexpr int E_COMP = E_ROWS * PE, H_COMP = H_ROWS * PE;
+    static constexpr int E_SLOT_BYTES = 3 * E_COMP * 4;
+    static constexpr int MAT_BYTES = H_ROWS * PM * static_cast<int>(sizeof(IdxT));
+    static constexpr int H_SLOT_BYTES = 3 * H_COMP * 4 + MAT_BYTES;
+    static constexpr int HB_BYTES = 3 * H_COMP * 4;
+    static constexpr int NE = 3, NH = 2;                        // ring depths
+    static constexpr size_t smem_bytes(int n_table_in_smem) {
+        return 128 + static_cast<size_t>(NE) * E_SLOT_BYTES + static_cast<size_t>(NH) * H_SLOT_BYTES + 2 * static_cast<size_t>(HB_BYTES) +
+               static_cast<size_t>(n_table_in_smem) * sizeof(float4);
+    }
+};
+
+template <int EXACT, typename IdxT, int BX, int BY>
+__global__ void __launch_bounds__(BX * BY, 2)
+k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const int zc) {
+    using LO = FusedLayout<IdxT, BX, BY>;
+    constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM, ME = LO::ME;
+    constexpr int E_COMP = LO::E_COMP, H_COMP = LO::H_COMP;
+    static_assert(LO::E_SLOT_BYTES % 16 == 0 && LO::H_SLOT_BYTES % 16 == 0 && LO::HB_BYTES % 16 == 0, "16-byte aligned slots");
+    static_assert(BX % 32 == 0, "warp 0 issues the copies");
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers
+    uint64_t* fullH = fullE + LO::NE;                              // 2 barriers
+    unsigned char* e_slots = smem_raw + 128;
+    unsigned char* h_slots = e_slots + LO::NE * LO::E_SLOT_BYTES;
+    float* hb = reinterpret_cast<float*>(h_slots + LO::NH * LO::H_SLOT_BYTES);   // 2 × 3 × H_COMP
+    float4* s_tab = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(hb) + 2 * LO::HB_BYTES);
+
+    const int tid = threadIdx.y * BX + threadIdx.x;
+    const unsigned lane = tid & 31u;
+    if (tid == 0) {
+        for (int s = 0; s < LO::NE; ++s) mbar_init(fullE + s, 1);
+        for (int s = 0; s < LO::NH; ++s) mbar_init(fullH + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (V.table_in_smem) {
+        for (int t = tid; t < V.n_table; t += NT) s_tab[t] = V.table[t];
+    }
+    __syncthreads();
+
+    const int x0 = blockIdx.x * (4 * BX);
+    const int y0 = blockIdx.y * BY;
+    const int za = blockIdx.z * zc;
+    const int zb = min(za + zc, V.nz);
+    const int n = zb - za;
+    const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
+    // forcing may hit the recomputed halo as well: test the extended box
+    bool has_src = false, has_probe = false;
+    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY + 1, za, zb + 1, V.nx, sz_ll)) != 0;
+    if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + BY, za, zb, V.nx, sz_ll)) != 0;
+    if (n <= 0) return;
+
+    const size_t sy = static_cast<size_t>(V.nx);
+    const size_t sz = sy * static_cast<size_t>(V.ny);
+    const int cols = min(4 * BX, V.nx - x0);
+    const int rows = min(BY, V.ny - y0);
+    const bool left = x0 > 0, right = x0 + 4 * BX < V.nx, low = y0 > 0, high = y0 + BY < V.ny;
+    const int last_h_plane = (zb < V.nz) ? zb : zb - 1;            // H'/old-E planes za..last_h_plane are needed
+    const int n_h = last_h_plane - za + 1;                          // number of H-plane iterations with a phase A
+
+    // ---- producers (warp 0) --------------------------------------------------------------------------------
+    const int e_rows_n = rows + (low ? 1 : 0) + (high ? 1 : 0);
+    const int h_rows_n = rows + (high ? 1 : 0);
+    const uint32_t e_row_bytes = static_cast<uint32_t>(cols + (left ? 4 : 0) + (right ? 4 : 0)) * 4u;
+    const uint32_t h_row_bytes = static_cast<uint32_t>(cols + (right ? 4 : 0)) * 4u;
+    const uint32_t m_row_bytes = static_cast<uint32_t>(cols + (right ? ME : 0)) * static_cast<uint32_t>(sizeof(IdxT));
+    auto issue_e = [&](int plane, int slot) {                       // called by all lanes of warp 0
+        uint64_t* bar = fullE + slot;
+        if (lane == 0) mbar_arrive_expect_tx(bar, 3u * static_cast<uint32_t>(e_rows_n) * e_row_bytes);
+        __syncwarp();
+        float* s = reinterpret_cast<float*>(e_slots + static_cast<size_t>(slot) * LO::E_SLOT_BYTES);
+        const long long base = static_cast<long long>(plane) * static_cast<long long>(sz) + static_cast<long long>(y0 - (low ? 1 : 0)) * static_cast<long long>(sy) +
+                               (x0 - (left ? 4 : 0));
+        for (int j = lane; j < 3 * e_rows_n; j += 32) {
+            const int c = j / e_rows_n, r = j - c * e_rows_n;         // r-th fetched row
+            const int srow = r + (low ? 0 : 1);
+            bulk_g2s(s + c * E_COMP + srow * PE + (left ? 0 : 4), V.in[c] + base + static_cast<long long>(r) * static_cast<long long>(sy), e_row_bytes, bar);
+        }
+    };
+    auto issue_h = [&](int plane, int slot) {
+        uint64_t* bar = fullH + slot;
+        if (lane == 0) mbar_arrive_expect_tx(bar, static_cast<uint32_t>(h_rows_n) * (3u * h_row_bytes + m_row_bytes));
+        __syncwarp();
+        unsigned char* sl = h_slots + static_cast<size_t>(slot) * LO::H_SLOT_BYTES;
+        float* s = reinterpret_cast<float*>(sl);
+        IdxT* sm = reinterpret_cast<IdxT*>(sl + 3 * H_COMP * 4);
+        const size_t base = static_cast<size_t>(plane) * sz + static_cast<size_t>(y0) * sy + static_cast<size_t>(x0);
+        for (int j = lane; j < 4 * h_rows_n; j += 32) {
+            const int c = j / h_rows_n, r = j - c * h_rows_n;
+            const size_t g = base + static_cast<size_t>(r) * sy;
+            if (c < 3) bulk_g2s(s + c * H_COMP + r * PE + 4, V.in[3 + c] + g, h_row_bytes, bar);
+            else bulk_g2s(sm + r * PM, static_cast<const IdxT*>(V.mat) + g, m_row_bytes, bar);
+        }
+    };
+    // E ring index of plane z: e = z - (za - 1); H ring index: k = z - za
+    if (tid < 32) {
+        if (za > 0) issue_e(za - 1, 0);
+        else if (lane == 0) mbar_arrive_expect_tx(fullE + 0, 0u);   // keep slot 0's phase sequence uniform (phase 0 completes empty)
+        issue_e(za, 1);
+        if (n_h > 1) issue_e(za + 1, 2);
+        issue_h(za, 0);
+        if (n_h > 1) issue_h(za + 1, 1);
+    }
+
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int x = x0 + 4 * tx, y = y0 + ty;
+    const bool act = (x < V.nx) && (y < V.ny);
+    // extra (halo) item of this thread for phase A: top row quads first, then the right column
+    const int n_extra = BX + BY;                                    // (quad j, row BY) for j < BX ; (quad BX, row j-BX) for the rest
+    int xq2 = -1, r2 = -1;
+    if (tid < n_extra) {
+        if (tid < BX) { xq2 = tid; r2 = BY; } else { xq2 = BX; r2 = tid - BX; }
+    }
+    const bool extra_ok = (xq2 >= 0) && (x0 + 4 * xq2 < V.nx) && (y0 + r2 < V.ny);
+
+    float4 hxo = make_float4(0.f, 0.f, 0.f, 0.f), hyo = hxo, hzo = hxo;   // H'(z_k) of the own quad
+    int mk_prev[4] = {0, 0, 0, 0};
+
+    for (int k = 0; k <= n; ++k) {
+        const int zk = za + k;
+        const bool has_a = k < n_h;
+        const float* e_cur = nullptr;
+        float4 hxn = hxo, hyn = hyo, hzn = hzo;
+        int mk_cur[4] = {0, 0, 0, 0};
+        if (has_a) {
+            const int e_idx = k + 1;
+            mbar_wait(fullE + (e_idx % LO::NE), static_cast<uint32_t>((e_idx / LO::NE) & 1));
+            mbar_wait(fullH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
+            if (k == 0 && za > 0) mbar_wait(fullE + 0, 0u);
+            e_cur = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(e_idx % LO::NE) * LO::E_SLOT_BYTES);
+            const float* e_low = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES);
+            const unsigned char* hsl = h_slots + static_cast<size_t>(k % LO::NH) * LO::H_SLOT_BYTES;
+            const float* h_old = reinterpret_cast<const float*>(hsl);
+            const IdxT* s_mat = reinterpret_cast<const IdxT*>(hsl + 3 * H_COMP * 4);
+            float* hb_w = hb + static_cast<size_t>(k & 1) * 3 * H_COMP;
+            const bool z_in = zk > 0;
+
+            // ---- phase A: H'(z_k) on the extended tile --------------------------------------------------------
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {
+                const int xq = pass == 0 ? tx : xq2;
+                const int r = pass == 0 ? ty : r2;
+                const bool ok = pass == 0 ? act : extra_ok;
+                if (pass == 1 && tid >= n_extra) break;
+                const int c0 = 4 + 4 * xq;
+                const int gx = x0 + 4 * xq, gy = y0 + r;
+                const float* pe = e_cur + (r + 1) * PE + c0;
+                const float4 ex = ld4(pe), ey = ld4(pe + E_COMP), ez = ld4(pe + 2 * E_COMP);
+                const float4 ex_ym = ld4(pe - PE), ez_ym = ld4(pe + 2 * E_COMP - PE);
+                const float ey_l = pe[E_COMP - 1], ez_l = pe[2 * E_COMP - 1];
+                const float* pl = e_low + (r + 1) * PE + c0;
+                const float4 ex_zm = ld4(pl), ey_zm = ld4(pl + E_COMP);
+                const float* ph = h_old + r * PE + c0;
+                float4 hx = ld4(ph), hy = ld4(ph + H_COMP), hz = ld4(ph + 2 * H_COMP);
+                int mk[4];
+                Idx4<IdxT>::load(s_mat, static_cast<size_t>(r) * PM + 4 * xq, mk);
+                if (!ok) { mk[0] = mk[1] = mk[2] = mk[3] = 0; }
+                const bool y_in = gy > 0, x_in = gx > 0;
+                const long long cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
+                int s0 = 0, cnt = 0;
+                if (has_src) {
+                    s0 = lower_bound_ll(F.cells, F.n, cell);
+                    while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
+                }
+                const float exv[4] = {ex.x, ex.y, ex.z, ex.w};
+                const float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
+                const float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
+                const float exym[4] = {ex_ym.x, ex_ym.y, ex_ym.z, ex_ym.w};
+                const float ezym[4] = {ez_ym.x, ez_ym.y, ez_ym.z, ez_ym.w};
+                const float exzm[4] = {ex_zm.x, ex_zm.y, ex_zm.z, ex_zm.w};
+                const float eyzm[4] = {ey_zm.x, ey_zm.y, ey_zm.z, ey_zm.w};
+                const float eyxm[4] = {ey_l, ey.x, ey.y, ey.z};
+                const float ezxm[4] = {ez_l, ez.x, ez.y, ez.z};
+                float hxv[4] = {hx.x, hx.y, hx.z, hx.w};
+                float hyv[4] = {hy.x, hy.y, hy.z, hy.w};
+                float hzv[4] = {hz.x, hz.y, hz.z, hz.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const bool xq_in = (q > 0) || x_in;
+                    const float dez_dy = y_in ? deriv<EXACT>(ezv[q], ezym[q], V.dx[1], V.inv_dx[1]) : 0.f;
+                    const float dex_dy = y_in ? deriv<EXACT>(exv[q], exym[q], V.dx[1], V.inv_dx[1]) : 0.f;
+                    const float dey_dz = z_in ? deriv<EXACT>(eyv[q], eyzm[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                    const float dex_dz = z_in ? deriv<EXACT>(exv[q], exzm[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                    const float dez_dx = xq_in ? deriv<EXACT>(ezv[q], ezxm[q], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float dey_dx = xq_in ? deriv<EXACT>(eyv[q], eyxm[q], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float cx = dez_dy - dey_dz;
+                    const float cy = dex_dz - dez_dx;
+                    const float cz = dey_dx - dex_dy;
+                    float mx = 0.f, my = 0.f, mz = 0.f;
+                    if (cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 3); mx = v.x; my = v.y; mz = v.z; }
+                    const float4 c = V.table_in_smem ? s_tab[mk[q]] : __ldg(V.table + mk[q]);
+                    hxv[q] = leap<EXACT>(c.z, hxv[q], c.w, -cx, mx);
+                    hyv[q] = leap<EXACT>(c.z, hyv[q], c.w, -cy, my);
+                    hzv[q] = leap<EXACT>(c.z, hzv[q], c.w, -cz, mz);
+                }
+                hx = make_float4(hxv[0], hxv[1], hxv[2], hxv[3]);
+                hy = make_float4(hyv[0], hyv[1], hyv[2], hyv[3]);
+                hz = make_float4(hzv[0], hzv[1], hzv[2], hzv[3]);
+                float* pw = hb_w + r * PE + c0;
+                st4(pw, hx); st4(pw + H_COMP, hy); st4(pw + 2 * H_COMP, hz);
+                if (pass == 0) {
+                    hxn = hx; hyn = hy; hzn = hz;
+                    mk_cur[0] = mk[0]; mk_cur[1] = mk[1]; mk_cur[2] = mk[2]; mk_cur[3] = mk[3];
+                    if (act && k < n) {                           // this CTA owns H' of its core planes
+                        const size_t gi = static_cast<size_t>(zk) * sz + static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
+                        st4(V.out[3] + gi, hx); st4(V.out[4] + gi, hy); st4(V.out[5] + gi, hz);
+                    }
+                }
+            }
+        }
+
+        // ---- phase B: E'(z_k - 1) on the core tile ----------------------------------------------------------------
+        if (k >= 1) {
+            const int zp = zk - 1;
+            const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (ty + 1) * PE + 4 + 4 * tx;
+            const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + 4 * tx;
+            float4 ex = ld4(e_own), ey = ld4(e_own + E_COMP), ez = ld4(e_own + 2 * E_COMP);
+            const float4 hz = hzo;
+            const float4 hz_yp = ld4(ph + 2 * H_COMP + PE), hx_yp = ld4(ph + PE);
+            const float hz_r = ph[2 * H_COMP + 4], hy_r = ph[H_COMP + 4];
+            const bool z_in = has_a;                                // H'(z_k) exists inside the lattice
+            const bool y_in = y + 1 < V.ny, x_in = x + 4 < V.nx;
+            const long long cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
+            int s0 = 0, cnt = 0;
+            if (has_src) {
+                s0 = lower_bound_ll(F.cells, F.n, cell);
+                while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
+            }
+            const float hxv[4] = {hxo.x, hxo.y, hxo.z, hxo.w};
+            const float hyv[4] = {hyo.x, hyo.y, hyo.z, hyo.w};
+            const float hzv[4] = {hz.x, hz.y, hz.z, hz.w};
+            const float hxzp[4] = {hxn.x, hxn.y, hxn.z, hxn.w};
+            const float hyzp[4] = {hyn.x, hyn.y, hyn.z, hyn.w};
+            const float hzyp[4] = {hz_yp.x, hz_yp.y, hz_yp.z, hz_yp.w};
+            const float hxyp[4] = {hx_yp.x, hx_yp.y, hx_yp.z, hx_yp.w};
+            const float hzxp[4] = {hz.y, hz.z, hz.w, hz_r};
+            const float hyxp[4] = {hyo.y, hyo.z, hyo.w, hy_r};
+            float exv[4] = {ex.x, ex.y, ex.z, ex.w};
+            float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
+            float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool xq_in = (q < 3) || x_in;
+                const float dhz_dy = y_in ? deriv<EXACT>(hzyp[q], hzv[q], V.dx[1], V.inv_dx[1]) : 0.f;
+                const float dhx_dy = y_in ? deriv<EXACT>(hxyp[q], hxv[q], V.dx[1], V.inv_dx[1]) : 0.f;
+                const float dhy_dz = z_in ? deriv<EXACT>(hyzp[q], hyv[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                const float dhx_dz = z_in ? deriv<EXACT>(hxzp[q], hxv[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                const float dhz_dx = xq_in ? deriv<EXACT>(hzxp[q], hzv[q], V.dx[0], V.inv_dx[0]) : 0.f;
+                const float dhy_dx = xq_in ? deriv<EXACT>(hyxp[q], hyv[q], V.dx[0], V.inv_dx[0]) : 0.f;
+                const float cx = dhz_dy - dhy_dz;
+                const float cy = dhx_dz - dhz_dx;
+                const float cz = dhy_dx - dhx_dy;
+                float jx = 0.f, jy = 0.f, jz = 0.f;
+                if (cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 0); jx = v.x; jy = v.y; jz = v.z; }
+                const float4 c = V.table_in_smem ? s_tab[mk_prev[q]] : __ldg(V.table + mk_prev[q]);
+                exv[q] = leap<EXACT>(c.x, exv[q], c.y, cx, jx);
+                eyv[q] = leap<EXACT>(c.x, eyv[q], c.y, cy, jy);
+                ezv[q] = leap<EXACT>(c.x, ezv[q], c.y, cz, jz);
+            }
+            ex = make_float4(exv[0], exv[1], exv[2], exv[3]);
+            ey = make_float4(eyv[0], eyv[1], eyv[2], eyv[3]);
+            ez = make_float4(ezv[0], ezv[1], ezv[2], ezv[3]);
+            if (act) {
+                const size_t gi = static_cast<size_t>(zp) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
+                st4(V.out[0] + gi, ex); st4(V.out[1] + gi, ey); st4(V.out[2] + gi, ez);
+                if (has_probe) {
+                    for (int s = lower_bound_ll(P.cells, P.n, cell); s < P.n; ++s) {
+                        const long long c = __ldg(P.cells + s);
+                        if (c >= cell + 4) break;
+                        const int q = static_cast<int>(c - cell);
+                        float* o = P.row + 6 * static_cast<size_t>(__ldg(P.slot + s));
+                        o[0] = pick(ex, q); o[1] = pick(ey, q); o[2] = pick(ez, q);
+                        o[3] = pick(hxo, q); o[4] = pick(hyo, q); o[5] = pick(hz, q);
+                    }
+                }
+            }
+        }
+        hxo = hxn; hyo = hyn; hzo = hzn;
+        mk_prev[0] = mk_cur[0]; mk_prev[1] = mk_cur[1]; mk_prev[2] = mk_cur[2]; mk_prev[3] = mk_cur[3];
+
+        __syncthreads();   // H'(z_k) tile complete; old-E plane z_k-1 and the old-H slot of z_k are drained
+        if (tid < 32) {
+            // E ring slot k % 3 held plane z_k - 1 → refill with plane z_k + 2; H ring slot k % 2 held z_k → z_k + 2
+            if (k + 2 < n_h) { issue_e(zk + 2, (k + 3) % LO::NE); issue_h(zk + 2, k % LO::NH); }
+        }
+    }
+}
+
+}  // namespace fdtd_b200

@@ -186,9 +186,10 @@ class FdtdB200Backend:
     """`SolverBackend<FdtdSolverConfig, Point3<usize>>` (lib.rs:28-45) for the CUDA engine."""
 
     def __init__(self, device: int = 0, exact_arithmetic: bool = False, force_generic_kernels: bool = False,
-                 z_slab: Optional[tuple] = None, probe_ring_steps: int = 0):
+                 z_slab: Optional[tuple] = None, probe_ring_steps: int = 0, fused_step: bool = False):
         self.device = int(device)
-        self.flags = (L.EXACT_ARITHMETIC if exact_arithmetic else 0) | (L.FORCE_GENERIC_KERNELS if force_generic_kernels else 0)
+        self.flags = ((L.EXACT_ARITHMETIC if exact_arithmetic else 0) | (L.FORCE_GENERIC_KERNELS if force_generic_kernels else 0)
+                      | (L.FUSED_STEP if fused_step else 0))
         self.z_slab = z_slab
         self.probe_ring_steps = int(probe_ring_steps)
 
@@ -434,6 +435,10 @@ class FdtdB200SolverState:
     @property
     def uses_vec4(self) -> bool:
         return bool(self._lib.fdtd_b200_uses_vec4(self._h))
+
+    @property
+    def uses_fused(self) -> bool:
+        return bool(self._lib.fdtd_b200_uses_fused(self._h))
 
     @property
     def uses_bulk(self) -> bool:

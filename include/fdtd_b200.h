@@ -48,7 +48,12 @@ enum {
        kernels multiply by 1/dx and let the compiler contract to FMA (documented in DESIGN.md). */
     FDTD_B200_EXACT_ARITHMETIC = 1u << 0,
     /* Force the one-thread-per-cell kernels even when nx % 4 == 0 (debugging / bisecting). */
-    FDTD_B200_FORCE_GENERIC_KERNELS = 1u << 1
+    FDTD_B200_FORCE_GENERIC_KERNELS = 1u << 1,
+    /* fdtd_b200_step() runs ONE fused kernel per step (H and E half-steps in a single pass over the lattice,
+       49 B instead of 74 B per cell update) on ping-pong field buffers: +24 B/cell of device memory.  Results are
+       bit-identical to the two-kernel path.  Ignored (two-kernel path) for z-slab handles and for lattices the
+       fused kernel does not support (nx not a multiple of 16 index bytes, nx < 128). */
+    FDTD_B200_FUSED_STEP = 1u << 2
 };
 
 /* cem-solver/src/material.rs:105-116 (same field order). */
@@ -164,6 +169,7 @@ double fdtd_b200_time(fdtd_b200_handle h);
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
 int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */
 int fdtd_b200_uses_bulk(fdtd_b200_handle h);     /* 1 when the TMA bulk-copy staged kernels run */
+int fdtd_b200_uses_fused(fdtd_b200_handle h);    /* 1 when fdtd_b200_step runs the fused single-pass kernel */
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h); /* kernels launched so far by this handle */
 /* Measurement: with profiling on, every H / E half-step launch is bracketed by CUDA events on the
  * handle's stream.  get_profile(which = 0 H | 1 E) blocks and returns the summed device time, the

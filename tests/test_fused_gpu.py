@@ -1,0 +1,102 @@
+"""GPU tests of the fused single-pass step (csrc/kernels_fused.cuh, FDTD_B200_FUSED_STEP): H and E half-steps in one
+kernel on ping-pong buffers must be bit-identical to the fp32 oracle (exact mode) and to the two-kernel path."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import oracle_run, random_fields
+from test_parity_gpu import _random_workload
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture
+def tune():
+    old = os.environ.get("FDTD_B200_TUNE")
+
+    def set_(v):
+        if v is None:
+            os.environ.pop("FDTD_B200_TUNE", None)
+        else:
+            os.environ["FDTD_B200_TUNE"] = v
+
+    yield set_
+    set_(old)
+
+
+def run(b200, w, steps, exact, fused, init=None, probes=None):
+    be = b200.FdtdB200Backend(exact_arithmetic=exact, fused_step=fused)
+    inst = be.create_instance(w.solver_config(), w.domain())
+    st = inst.create_state()
+    if init is not None:
+        st.write_field(b200.FieldComponent.E, init[0])
+        st.write_field(b200.FieldComponent.H, init[1])
+    if probes:
+        st.register_probes(probes)
+    if w.sources:
+        st.set_source_table(w.source_points(), w.source_table(steps))
+    st.step(steps)
+    return st, (st.read_probes(0, steps) if probes else None)
+
+
+@pytest.mark.parametrize("size,zc", [
+    ((128, 8, 6), 0), ((128, 9, 7), 3), ((128, 1, 1), 0), ((256, 5, 20), 7), ((144, 17, 9), 4), ((512, 20, 5), 2),
+    ((272, 8, 70), 0), ((128, 16, 2), 1),
+])
+def test_fused_step_bit_identical_to_f32_oracle(b200, oracle, tune, size, zc):
+    tune(f"0,0,{zc},-1,0")
+    w = _random_workload(b200, size, seed=sum(size) + 3)
+    # a second source right at a tile corner so that the recomputed halo H' sees its m forcing
+    w.sources.append(((min(127, size[0] - 1), min(7, size[1] - 1), size[2] // 2), b200.GaussianPulse(0.3, 0.4).with_amplitudes((0.5, 1.5, -2.0), (3.0, -1.0, 0.25))))
+    init = random_fields(w, seed=10)
+    probes = [(size[0] // 2, size[1] // 2, size[2] // 2), (0, 0, 0), (size[0] - 1, size[1] - 1, size[2] - 1), (min(128, size[0] - 1), min(8, size[1] - 1), 0)]
+    steps = 5                                        # odd: the result lives in the second buffer set
+    ref, s32 = oracle_run(oracle, w, steps, oracle.F32, init=init, probes=probes)
+    st, series = run(b200, w, steps, exact=True, fused=True, init=init, probes=probes)
+    assert st.uses_fused
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
+    assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.field(oracle.H).astype(np.float32))
+    assert np.array_equal(series, s32.astype(np.float32))
+    assert st.tick() == steps and st.kernel_launches < 2 * steps + 10
+
+
+def test_fused_fast_mode_equals_two_kernel_path(b200, tune):
+    from fdtd_b200 import configs
+
+    tune(None)
+    w = configs.config3_heterogeneous(128, 40)
+    a, _ = run(b200, w, 40, exact=False, fused=True)
+    b, _ = run(b200, w, 40, exact=False, fused=False)
+    assert a.uses_fused and not b.uses_fused
+    assert np.array_equal(a.read_field(b200.FieldComponent.E), b.read_field(b200.FieldComponent.E))
+    assert np.array_equal(a.read_field(b200.FieldComponent.H), b.read_field(b200.FieldComponent.H))
+    # continue stepping both one update pass at a time (reference protocol) and through reset
+    for st in (a, b):
+        st.step(3)
+    assert np.array_equal(a.read_field(b200.FieldComponent.E), b.read_field(b200.FieldComponent.E))
+    a.reset()
+    assert not np.any(a.read_field(b200.FieldComponent.E)) and a.tick() == 0
+
+
+def test_fused_u16_index_and_fallbacks(b200, oracle, tune):
+    from fdtd_b200 import configs
+
+    tune(None)
+    rng = np.random.default_rng(12)
+    n_mat = 300
+    pal = [b200.Material(1.0 + 0.001 * k, 0.0, 1.0 + 0.01 * k, 0.001 * (k % 5)) for k in range(n_mat)]
+    size = (128, 6, 5)
+    ids = rng.integers(0, n_mat, size[0] * size[1] * size[2]).astype(np.uint32)
+    w = configs.Workload("u16f", size, b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED, pal, ids,
+                         [((64, 3, 2), b200.GaussianPulse(1.0, 1.0).with_amplitudes((0, 0, 5.0), (0, 0, 0)))], [], 0)
+    init = random_fields(w, seed=13)
+    ref, _ = oracle_run(oracle, w, 4, oracle.F32, init=init)
+    st, _ = run(b200, w, 4, exact=True, fused=True, init=init)
+    assert st.uses_fused and st.index_bytes == 2
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
+    assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.field(oracle.H).astype(np.float32))
+    # lattices the fused kernel does not support silently use the two-kernel path
+    w2 = _random_workload(b200, (36, 5, 4), seed=2)
+    st2, _ = run(b200, w2, 2, exact=True, fused=True)
+    assert not st2.uses_fused and st2.tick() == 2
