@@ -48,6 +48,9 @@ struct fdtd_b200_solver {
     float* alt_alloc[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // ping-pong set of the fused step
     float* g[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool fused = false;
+    FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
+    bool fused_maps_ready = false;
+    int cur_set = 0;                // which buffer set f[] currently points at
     void* mat = nullptr;
     int idx_bytes = 1;
     float4* table = nullptr;
@@ -363,10 +366,50 @@ bool fused_eligible(const fdtd_b200_config& cfg, uint64_t nzl, int idx_bytes, bo
     return whole && vec4 && (cfg.nx * idx_bytes) % 16 == 0 && cfg.nx >= 128;
 }
 
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 3-D map (x, y, z) of one lattice array with a box of (bx, by, 1) elements
+int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_t elem, void* base, uint32_t bx, uint32_t by) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail(h, FDTD_B200_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[3] = {h->nx, h->ny, h->nzl};
+    const cuuint64_t strides[2] = {h->nx * elem, h->nx * h->ny * elem};
+    const cuuint32_t box[3] = {bx, by, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(out, dt, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, FDTD_B200_ECUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r)));
+    return FDTD_B200_OK;
+}
+
 template <int EXACT, typename IdxT>
 int launch_fused_t(fdtd_b200_handle h) {
     constexpr int BX = 32, BY = 8;
     using LO = FusedLayout<IdxT, BX, BY>;
+    if (!h->fused_maps_ready) {
+        for (int set = 0; set < 2; ++set) {
+            float* const* arr = (set == h->cur_set) ? h->f : h->g;
+            for (int c = 0; c < 3; ++c) {
+                if (int rc = make_map(h, &h->fused_maps[set].e[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[c], LO::PE, LO::E_ROWS)) return rc;
+                if (int rc = make_map(h, &h->fused_maps[set].h[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[3 + c], LO::PE, LO::H_ROWS)) return rc;
+            }
+            if (int rc = make_map(h, &h->fused_maps[set].mat, sizeof(IdxT) == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
+                                  sizeof(IdxT), h->mat, LO::PM, LO::H_ROWS)) return rc;
+        }
+        h->fused_maps_ready = true;
+    }
     FusedView V{};
     for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
     V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table);
@@ -377,16 +420,16 @@ int launch_fused_t(fdtd_b200_handle h) {
     const ProbeView P = probe_view(h);
     int zc = h->tune.zc;
     if (zc <= 0) {
-        const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + BY - 1) / BY);
+        const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS);
         zc = 64;
         while (zc > 8 && tiles * ((V.nz + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
     }
     dim3 block(BX, BY, 1);
-    dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + BY - 1) / BY, (V.nz + zc - 1) / zc);
+    dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (V.nz + zc - 1) / zc);
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0);
     auto k = k_step_fused<EXACT, IdxT, BX, BY>;
     CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    k<<<grid, block, smem, h->stream>>>(V, F, P, zc);
+    k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
@@ -459,6 +502,7 @@ int launch_fused(fdtd_b200_handle h) {
     if (rc) return rc;
     if (int rc2 = prof_end(h, 0)) return rc2;
     for (int c = 0; c < 6; ++c) { std::swap(h->f[c], h->g[c]); std::swap(h->alloc[c], h->alt_alloc[c]); }
+    h->cur_set ^= 1;
     return FDTD_B200_OK;
 }
 

@@ -3,19 +3,38 @@
 // fdtd/wgpu/update.wgsl:56-177), so a cell update moves 6 fp32 reads + 6 fp32 writes + 1 B index = 49 B instead of 74 B.
 //
 // E'(p) needs H' at p, p+x, p+y, p+z, and a neighbouring CTA cannot see this CTA's fresh H' in time, so every CTA
-// recomputes H' on its tile extended by one column, one row and one plane (overlapped tiling).  That recomputation reads
+// recomputes H' one row, one column and one plane beyond the cells whose E' it owns (overlapped tiling): a CTA of BY
+// thread rows computes H' on BY rows and E' on the lower BY-1 of them (tiles advance by BY-1 rows; the top thread row
+// has no E' work and is the TMA producer instead), and every row also computes the single H'y,H'z cell to its right.  That recomputation reads
 // the OLD fields of cells another CTA is updating, hence the step is out of place: fields are ping-pong buffered
 // (in → out) and the handle swaps the two sets after the launch.
 //
 // Data movement: old E (3 planes resident: z-1, z, z+1 in flight) and old H + material index (2 planes) are streamed
-// into shared-memory rings by 1-D TMA bulk copies (UBLKCP) completing on mbarriers; the fresh H' of two consecutive
+// into shared-memory rings by 3-D TMA tensor copies (cp.async.bulk.tensor.3d, one box per component and plane — SASS
+// UTMALDG; out-of-lattice halo elements are zero-filled by the TMA unit) completing on mbarriers; the fresh H' of two consecutive
 // planes is exchanged between threads through a double-buffered shared-memory tile.  One __syncthreads per plane.
 // Arithmetic = the helpers of kernels.cuh → bit-identical to the two-kernel path.
 #pragma once
 
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched with cudaGetDriverEntryPoint)
+
 #include "kernels_bulk.cuh"
 
 namespace fdtd_b200 {
+
+// Tensor maps of the step's input arrays (3-D: x, y, z; boxes of one plane of a CTA tile incl. halos).
+struct FusedMaps {
+    CUtensorMap e[3];   // old Ex, Ey, Ez : box (PE, E_ROWS, 1)
+    CUtensorMap h[3];   // old Hx, Hy, Hz : box (PE, H_ROWS, 1)
+    CUtensorMap mat;    // material index : box (PM, H_ROWS, 1)
+};
+
+__device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(map), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 struct FusedView {
     const float* in[6];   // Ex Ey Ez Hx Hy Hz of the current step (plane 0)
@@ -33,10 +52,14 @@ struct FusedLayout {
     static constexpr int PE = 4 * BX + 8;                       // field row pitch: [left halo quad][4*BX cells][right halo quad]
     static constexpr int ME = 16 / static_cast<int>(sizeof(IdxT));  // extra index entries fetched to the right (16 bytes)
     static constexpr int PM = 4 * BX + ME;                      // index row pitch (entries)
-    static constexpr int E_ROWS = BY + 2, H_ROWS = BY + 1;
-    static constexpr int E_COMP = E_ROWS * PE, H_COMP = H_ROWS * PE;
+    static constexpr int CORE_ROWS = BY - 1;                    // rows whose E' this CTA owns
+    static constexpr int E_ROWS = BY + 1, H_ROWS = BY;          // old E: rows y0-1 .. y0+BY-1 ; H: rows y0 .. y0+BY-1
+    // component strides are padded to 128 bytes: TMA tensor copies need 128-byte aligned shared-memory destinations
+    static constexpr int E_COMP = (E_ROWS * PE + 31) / 32 * 32, H_COMP = (H_ROWS * PE + 31) / 32 * 32;
+    static constexpr int E_BOX_BYTES = E_ROWS * PE * 4, H_BOX_BYTES = H_ROWS * PE * 4;
+    static constexpr int M_BOX_BYTES = H_ROWS * PM * static_cast<int>(sizeof(IdxT));
     static constexpr int E_SLOT_BYTES = 3 * E_COMP * 4;
-    static constexpr int MAT_BYTES = H_ROWS * PM * static_cast<int>(sizeof(IdxT));
+    static constexpr int MAT_BYTES = (M_BOX_BYTES + 127) / 128 * 128;
     static constexpr int H_SLOT_BYTES = 3 * H_COMP * 4 + MAT_BYTES;
     static constexpr int HB_BYTES = 3 * H_COMP * 4;
     static constexpr int NE = 3, NH = 2;                        // ring depths
@@ -48,11 +71,11 @@ struct FusedLayout {
 
 template <int EXACT, typename IdxT, int BX, int BY>
 __global__ void __launch_bounds__(BX * BY, 2)
-k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const int zc) {
+k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const ForcingView F, const ProbeView P, const int zc) {
     using LO = FusedLayout<IdxT, BX, BY>;
-    constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM, ME = LO::ME;
+    constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM;
     constexpr int E_COMP = LO::E_COMP, H_COMP = LO::H_COMP;
-    static_assert(LO::E_SLOT_BYTES % 16 == 0 && LO::H_SLOT_BYTES % 16 == 0 && LO::HB_BYTES % 16 == 0, "16-byte aligned slots");
+    static_assert(LO::E_SLOT_BYTES % 128 == 0 && LO::H_SLOT_BYTES % 128 == 0 && LO::HB_BYTES % 128 == 0, "128-byte aligned slots");
     static_assert(BX % 32 == 0, "warp 0 issues the copies");
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -77,61 +100,47 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
     __syncthreads();
 
     const int x0 = blockIdx.x * (4 * BX);
-    const int y0 = blockIdx.y * BY;
+    const int y0 = blockIdx.y * LO::CORE_ROWS;
     const int za = blockIdx.z * zc;
     const int zb = min(za + zc, V.nz);
     const int n = zb - za;
     const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
     // forcing may hit the recomputed halo as well: test the extended box
     bool has_src = false, has_probe = false;
-    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY + 1, za, zb + 1, V.nx, sz_ll)) != 0;
-    if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + BY, za, zb, V.nx, sz_ll)) != 0;
+    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY, za, zb + 1, V.nx, sz_ll)) != 0;
+    if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + LO::CORE_ROWS, za, zb, V.nx, sz_ll)) != 0;
     if (n <= 0) return;
 
     const size_t sy = static_cast<size_t>(V.nx);
     const size_t sz = sy * static_cast<size_t>(V.ny);
-    const int cols = min(4 * BX, V.nx - x0);
-    const int rows = min(BY, V.ny - y0);
-    const bool left = x0 > 0, right = x0 + 4 * BX < V.nx, low = y0 > 0, high = y0 + BY < V.ny;
+    const bool right = x0 + 4 * BX < V.nx;
     const int last_h_plane = (zb < V.nz) ? zb : zb - 1;            // H'/old-E planes za..last_h_plane are needed
     const int n_h = last_h_plane - za + 1;                          // number of H-plane iterations with a phase A
 
-    // ---- producers (warp 0) --------------------------------------------------------------------------------
-    const int e_rows_n = rows + (low ? 1 : 0) + (high ? 1 : 0);
-    const int h_rows_n = rows + (high ? 1 : 0);
-    const uint32_t e_row_bytes = static_cast<uint32_t>(cols + (left ? 4 : 0) + (right ? 4 : 0)) * 4u;
-    const uint32_t h_row_bytes = static_cast<uint32_t>(cols + (right ? 4 : 0)) * 4u;
-    const uint32_t m_row_bytes = static_cast<uint32_t>(cols + (right ? ME : 0)) * static_cast<uint32_t>(sizeof(IdxT));
-    auto issue_e = [&](int plane, int slot) {                       // called by all lanes of warp 0
-        uint64_t* bar = fullE + slot;
-        if (lane == 0) mbar_arrive_expect_tx(bar, 3u * static_cast<uint32_t>(e_rows_n) * e_row_bytes);
-        __syncwarp();
-        float* s = reinterpret_cast<float*>(e_slots + static_cast<size_t>(slot) * LO::E_SLOT_BYTES);
-        const long long base = static_cast<long long>(plane) * static_cast<long long>(sz) + static_cast<long long>(y0 - (low ? 1 : 0)) * static_cast<long long>(sy) +
-                               (x0 - (left ? 4 : 0));
-        for (int j = lane; j < 3 * e_rows_n; j += 32) {
-            const int c = j / e_rows_n, r = j - c * e_rows_n;         // r-th fetched row
-            const int srow = r + (low ? 0 : 1);
-            bulk_g2s(s + c * E_COMP + srow * PE + (left ? 0 : 4), V.in[c] + base + static_cast<long long>(r) * static_cast<long long>(sy), e_row_bytes, bar);
+    // ---- producer: one lane of the last warp issues 7 tensor copies per plane ------------------------------------
+    auto issue_e = [&](int plane, int slot) {
+        if (lane == 0) {
+            uint64_t* bar = fullE + slot;
+            mbar_arrive_expect_tx(bar, 3u * LO::E_BOX_BYTES);
+            float* s = reinterpret_cast<float*>(e_slots + static_cast<size_t>(slot) * LO::E_SLOT_BYTES);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * E_COMP, &M.e[c], x0 - 4, y0 - 1, plane, bar);
         }
     };
     auto issue_h = [&](int plane, int slot) {
-        uint64_t* bar = fullH + slot;
-        if (lane == 0) mbar_arrive_expect_tx(bar, static_cast<uint32_t>(h_rows_n) * (3u * h_row_bytes + m_row_bytes));
-        __syncwarp();
-        unsigned char* sl = h_slots + static_cast<size_t>(slot) * LO::H_SLOT_BYTES;
-        float* s = reinterpret_cast<float*>(sl);
-        IdxT* sm = reinterpret_cast<IdxT*>(sl + 3 * H_COMP * 4);
-        const size_t base = static_cast<size_t>(plane) * sz + static_cast<size_t>(y0) * sy + static_cast<size_t>(x0);
-        for (int j = lane; j < 4 * h_rows_n; j += 32) {
-            const int c = j / h_rows_n, r = j - c * h_rows_n;
-            const size_t g = base + static_cast<size_t>(r) * sy;
-            if (c < 3) bulk_g2s(s + c * H_COMP + r * PE + 4, V.in[3 + c] + g, h_row_bytes, bar);
-            else bulk_g2s(sm + r * PM, static_cast<const IdxT*>(V.mat) + g, m_row_bytes, bar);
+        if (lane == 0) {
+            uint64_t* bar = fullH + slot;
+            mbar_arrive_expect_tx(bar, 3u * LO::H_BOX_BYTES + LO::M_BOX_BYTES);
+            unsigned char* sl = h_slots + static_cast<size_t>(slot) * LO::H_SLOT_BYTES;
+            float* s = reinterpret_cast<float*>(sl);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * H_COMP, &M.h[c], x0 - 4, y0, plane, bar);
+            tma_load_3d(sl + 3 * H_COMP * 4, &M.mat, x0, y0, plane, bar);
         }
     };
     // E ring index of plane z: e = z - (za - 1); H ring index: k = z - za
-    if (tid < 32) {
+    const bool producer = tid >= NT - 32;                           // the last warp: it has no E' work (top thread row)
+    if (producer) {
         if (za > 0) issue_e(za - 1, 0);
         else if (lane == 0) mbar_arrive_expect_tx(fullE + 0, 0u);   // keep slot 0's phase sequence uniform (phase 0 completes empty)
         issue_e(za, 1);
@@ -143,13 +152,7 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int x = x0 + 4 * tx, y = y0 + ty;
     const bool act = (x < V.nx) && (y < V.ny);
-    // extra (halo) item of this thread for phase A: top row quads first, then the right column
-    const int n_extra = BX + BY;                                    // (quad j, row BY) for j < BX ; (quad BX, row j-BX) for the rest
-    int xq2 = -1, r2 = -1;
-    if (tid < n_extra) {
-        if (tid < BX) { xq2 = tid; r2 = BY; } else { xq2 = BX; r2 = tid - BX; }
-    }
-    const bool extra_ok = (xq2 >= 0) && (x0 + 4 * xq2 < V.nx) && (y0 + r2 < V.ny);
+    const bool core = act && (ty < LO::CORE_ROWS);                  // this thread owns E' of its quad
 
     float4 hxo = make_float4(0.f, 0.f, 0.f, 0.f), hyo = hxo, hzo = hxo;   // H'(z_k) of the own quad
     int mk_prev[4] = {0, 0, 0, 0};
@@ -173,13 +176,10 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
             float* hb_w = hb + static_cast<size_t>(k & 1) * 3 * H_COMP;
             const bool z_in = zk > 0;
 
-            // ---- phase A: H'(z_k) on the extended tile --------------------------------------------------------
-#pragma unroll 1
-            for (int pass = 0; pass < 2; ++pass) {
-                const int xq = pass == 0 ? tx : xq2;
-                const int r = pass == 0 ? ty : r2;
-                const bool ok = pass == 0 ? act : extra_ok;
-                if (pass == 1 && tid >= n_extra) break;
+            // ---- phase A: H'(z_k) on the CTA's BY rows -----------------------------------------------------------
+            {
+                const int xq = tx, r = ty;
+                const bool ok = act;
                 const int c0 = 4 + 4 * xq;
                 const int gx = x0 + 4 * xq, gy = y0 + r;
                 const float* pe = e_cur + (r + 1) * PE + c0;
@@ -236,19 +236,48 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
                 hz = make_float4(hzv[0], hzv[1], hzv[2], hzv[3]);
                 float* pw = hb_w + r * PE + c0;
                 st4(pw, hx); st4(pw + H_COMP, hy); st4(pw + 2 * H_COMP, hz);
-                if (pass == 0) {
+                {
                     hxn = hx; hyn = hy; hzn = hz;
                     mk_cur[0] = mk[0]; mk_cur[1] = mk[1]; mk_cur[2] = mk[2]; mk_cur[3] = mk[3];
-                    if (act && k < n) {                           // this CTA owns H' of its core planes
+                    if (core && k < n) {                          // this CTA owns H' of its core rows and planes
                         const size_t gi = static_cast<size_t>(zk) * sz + static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
                         st4(V.out[3] + gi, hx); st4(V.out[4] + gi, hy); st4(V.out[5] + gi, hz);
                     }
                 }
             }
+            // H'y, H'z of the single cell to the right of each row (x1 = x0 + 4*BX): phase B's d/dx of the row's last cell.
+            // Every lane of the row computes the same value (broadcast reads); one lane writes it.
+            if (right) {
+                const int r = ty, cR = 4 + 4 * BX;
+                const int gy = y0 + r, gx = x0 + 4 * BX;
+                const float* pe = e_cur + (r + 1) * PE + cR;
+                const float ex = pe[0], ex_ym = pe[-PE], ey = pe[E_COMP], ey_l = pe[E_COMP - 1], ez = pe[2 * E_COMP], ez_l = pe[2 * E_COMP - 1];
+                const float ex_zm = e_low[(r + 1) * PE + cR];
+                const float hy = h_old[H_COMP + r * PE + cR], hz = h_old[2 * H_COMP + r * PE + cR];
+                int m1 = static_cast<int>(s_mat[static_cast<size_t>(r) * PM + 4 * BX]);
+                if (gy >= V.ny) m1 = 0;
+                const bool y_in = gy > 0;
+                const float dex_dz = z_in ? deriv<EXACT>(ex, ex_zm, V.dx[2], V.inv_dx[2]) : 0.f;
+                const float dez_dx = deriv<EXACT>(ez, ez_l, V.dx[0], V.inv_dx[0]);
+                const float dey_dx = deriv<EXACT>(ey, ey_l, V.dx[0], V.inv_dx[0]);
+                const float dex_dy = y_in ? deriv<EXACT>(ex, ex_ym, V.dx[1], V.inv_dx[1]) : 0.f;
+                const float cy = dex_dz - dez_dx;
+                const float cz = dey_dx - dex_dy;
+                float my = 0.f, mz = 0.f;
+                if (has_src) {
+                    const long long cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
+                    const int s1 = lower_bound_ll(F.cells, F.n, cell);
+                    if (s1 < F.n && __ldg(F.cells + s1) == cell) { my = __ldg(F.vals + 6 * s1 + 4); mz = __ldg(F.vals + 6 * s1 + 5); }
+                }
+                const float4 c = V.table_in_smem ? s_tab[m1] : __ldg(V.table + m1);
+                const float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
+                const float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
+                if (tx == 0) { hb_w[H_COMP + r * PE + cR] = hy1; hb_w[2 * H_COMP + r * PE + cR] = hz1; }
+            }
         }
 
         // ---- phase B: E'(z_k - 1) on the core tile ----------------------------------------------------------------
-        if (k >= 1) {
+        if (k >= 1 && ty < LO::CORE_ROWS) {
             const int zp = zk - 1;
             const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (ty + 1) * PE + 4 + 4 * tx;
             const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + 4 * tx;
@@ -298,7 +327,7 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
             ex = make_float4(exv[0], exv[1], exv[2], exv[3]);
             ey = make_float4(eyv[0], eyv[1], eyv[2], eyv[3]);
             ez = make_float4(ezv[0], ezv[1], ezv[2], ezv[3]);
-            if (act) {
+            if (core) {
                 const size_t gi = static_cast<size_t>(zp) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
                 st4(V.out[0] + gi, ex); st4(V.out[1] + gi, ey); st4(V.out[2] + gi, ez);
                 if (has_probe) {
@@ -317,10 +346,8 @@ k_step_fused(const FusedView V, const ForcingView F, const ProbeView P, const in
         mk_prev[0] = mk_cur[0]; mk_prev[1] = mk_cur[1]; mk_prev[2] = mk_cur[2]; mk_prev[3] = mk_cur[3];
 
         __syncthreads();   // H'(z_k) tile complete; old-E plane z_k-1 and the old-H slot of z_k are drained
-        if (tid < 32) {
-            // E ring slot k % 3 held plane z_k - 1 → refill with plane z_k + 2; H ring slot k % 2 held z_k → z_k + 2
-            if (k + 2 < n_h) { issue_e(zk + 2, (k + 3) % LO::NE); issue_h(zk + 2, k % LO::NH); }
-        }
+        // E ring slot k % 3 held plane z_k - 1 → refill with plane z_k + 2; H ring slot k % 2 held z_k → z_k + 2
+        if (producer && k + 2 < n_h) { issue_e(zk + 2, (k + 3) % LO::NE); issue_h(zk + 2, k % LO::NH); }
     }
 }
 
