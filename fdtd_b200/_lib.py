@@ -14,7 +14,10 @@ FORCE_GENERIC_KERNELS = 1 << 1
 FUSED_STEP = 1 << 2
 COLORMAP_CPU, COLORMAP_LINEAR, COLORMAP_APP_Z = 0, 1, 2
 (HALO_SEND_EX_TOP, HALO_SEND_EY_TOP, HALO_RECV_EX_LOW, HALO_RECV_EY_LOW,
- HALO_SEND_HX_BOTTOM, HALO_SEND_HY_BOTTOM, HALO_RECV_HX_HIGH, HALO_RECV_HY_HIGH) = range(8)
+ HALO_SEND_HX_BOTTOM, HALO_SEND_HY_BOTTOM, HALO_RECV_HX_HIGH, HALO_RECV_HY_HIGH,
+ HALO_SEND_EX_BOTTOM, HALO_SEND_EY_BOTTOM, HALO_SEND_EZ_BOTTOM, HALO_RECV_EX_HIGH, HALO_RECV_EY_HIGH, HALO_RECV_EZ_HIGH,
+ HALO_SEND_MAT_BOTTOM, HALO_RECV_MAT_HIGH) = range(16)
+HALO_PENDING = 0x100
 
 
 class Material(C.Structure):
@@ -84,6 +87,8 @@ SYMBOLS = {
     "fdtd_b200_update_h": (C.c_int, [_H, C.c_uint64, C.c_uint64]),
     "fdtd_b200_update_e": (C.c_int, [_H, C.c_uint64, C.c_uint64]),
     "fdtd_b200_end_step": (C.c_int, [_H]),
+    "fdtd_b200_fused_update": (C.c_int, [_H, C.c_uint64, C.c_uint64]),
+    "fdtd_b200_fused_commit": (C.c_int, [_H]),
     "fdtd_b200_halo_plane": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p), _u64p]),
     "fdtd_b200_halo_copy": (C.c_int, [_H, C.c_int, _H, C.c_int]),
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),

@@ -362,8 +362,8 @@ bool use_bulk(fdtd_b200_handle h) {
 
 // ---- fused single-pass step (kernels_fused.cuh) --------------------------------------------------------
 bool fused_eligible(const fdtd_b200_config& cfg, uint64_t nzl, int idx_bytes, bool vec4) {
-    const bool whole = (cfg.z_begin == 0) && (cfg.z_end == 0 || cfg.z_end == cfg.nz) && nzl == cfg.nz;
-    return whole && vec4 && (cfg.nx * idx_bytes) % 16 == 0 && cfg.nx >= 128;
+    (void)nzl;
+    return vec4 && (cfg.nx * idx_bytes) % 16 == 0 && cfg.nx >= 128;
 }
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -381,10 +381,10 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 // 3-D map (x, y, z) of one lattice array with a box of (bx, by, 1) elements
-int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_t elem, void* base, uint32_t bx, uint32_t by) {
+int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_t elem, void* base, uint32_t bx, uint32_t by, uint64_t extra_planes) {
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return fail(h, FDTD_B200_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    const cuuint64_t dims[3] = {h->nx, h->ny, h->nzl};
+    const cuuint64_t dims[3] = {h->nx, h->ny, h->nzl + extra_planes};
     const cuuint64_t strides[2] = {h->nx * elem, h->nx * h->ny * elem};
     const cuuint32_t box[3] = {bx, by, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
@@ -395,18 +395,18 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
 }
 
 template <int EXACT, typename IdxT>
-int launch_fused_t(fdtd_b200_handle h) {
+int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     constexpr int BX = 32, BY = 8;
     using LO = FusedLayout<IdxT, BX, BY>;
     if (!h->fused_maps_ready) {
         for (int set = 0; set < 2; ++set) {
-            float* const* arr = (set == h->cur_set) ? h->f : h->g;
+            float* const* arr = (set == h->cur_set) ? h->alloc : h->alt_alloc;   // maps start at the lower ghost plane
             for (int c = 0; c < 3; ++c) {
-                if (int rc = make_map(h, &h->fused_maps[set].e[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[c], LO::PE, LO::E_ROWS)) return rc;
-                if (int rc = make_map(h, &h->fused_maps[set].h[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[3 + c], LO::PE, LO::H_ROWS)) return rc;
+                if (int rc = make_map(h, &h->fused_maps[set].e[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[c], LO::PE, LO::E_ROWS, 2)) return rc;
+                if (int rc = make_map(h, &h->fused_maps[set].h[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[3 + c], LO::PE, LO::H_ROWS, 2)) return rc;
             }
             if (int rc = make_map(h, &h->fused_maps[set].mat, sizeof(IdxT) == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
-                                  sizeof(IdxT), h->mat, LO::PM, LO::H_ROWS)) return rc;
+                                  sizeof(IdxT), h->mat, LO::PM, LO::H_ROWS, 1)) return rc;   // + the upper neighbour's first plane
         }
         h->fused_maps_ready = true;
     }
@@ -415,6 +415,9 @@ int launch_fused_t(fdtd_b200_handle h) {
     V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table);
     V.table_in_smem = h->n_table <= 64 ? 1 : 0;
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
+    V.z_lo = z_lo; V.z_hi = z_hi;
+    V.lo_open = h->z_begin > 0 ? 1 : 0;
+    V.hi_open = h->z_end < h->nz ? 1 : 0;
     for (int a = 0; a < 3; ++a) { V.dx[a] = static_cast<float>(h->cfg.dx[a]); V.inv_dx[a] = 1.0f / V.dx[a]; }
     const ForcingView F = forcing_view(h);
     const ProbeView P = probe_view(h);
@@ -422,10 +425,10 @@ int launch_fused_t(fdtd_b200_handle h) {
     if (zc <= 0) {
         const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS);
         zc = 64;
-        while (zc > 8 && tiles * ((V.nz + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
+        while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
     }
     dim3 block(BX, BY, 1);
-    dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (V.nz + zc - 1) / zc);
+    dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0);
     auto k = k_step_fused<EXACT, IdxT, BX, BY>;
     CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -493,17 +496,22 @@ void prof_clear(fdtd_b200_handle h) {
     }
 }
 
-int launch_fused(fdtd_b200_handle h) {
+// planes [z_lo, z_hi) of the current set → the pending set (no swap)
+int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi) {
+    if (z_lo >= z_hi) return FDTD_B200_OK;
     const int mode = arithmetic_mode(h);
-    if (int rc = prof_begin(h, 0, static_cast<int>(h->nzl))) return rc;
+    if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h) : (mode == 1 ? launch_fused_t<1, uint8_t>(h) : launch_fused_t<2, uint8_t>(h));
-    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h) : (mode == 1 ? launch_fused_t<1, uint16_t>(h) : launch_fused_t<2, uint16_t>(h));
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi));
+    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
-    if (int rc2 = prof_end(h, 0)) return rc2;
+    return prof_end(h, 0);
+}
+
+// the pending set becomes the current one
+void commit_fused(fdtd_b200_handle h) {
     for (int c = 0; c < 6; ++c) { std::swap(h->f[c], h->g[c]); std::swap(h->alloc[c], h->alt_alloc[c]); }
     h->cur_set ^= 1;
-    return FDTD_B200_OK;
 }
 
 void end_step(fdtd_b200_handle h) {
@@ -598,10 +606,9 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
         }
     }
     // material index (+8 bytes slack so the last quad's vector load never leaves the allocation)
-    CU_NEW(cudaMalloc(&h->mat, h->n_local * h->idx_bytes + 16));
-    if (!material_ids) {
-        CU_NEW(cudaMemsetAsync(h->mat, 0, h->n_local * h->idx_bytes + 16, h->stream));
-    } else {
+    CU_NEW(cudaMalloc(&h->mat, (h->n_local + h->plane) * h->idx_bytes + 16));
+    CU_NEW(cudaMemsetAsync(h->mat, 0, (h->n_local + h->plane) * h->idx_bytes + 16, h->stream));
+    if (material_ids) {
         // stream the u32 ids through a bounded staging buffer and narrow them on the device
         const size_t chunk = std::min<size_t>(h->n_local, size_t(1) << 24);
         uint32_t* d_ids = nullptr;
@@ -735,7 +742,7 @@ size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_byt
     // 80 B/cell wgpu/mod.rs:129-133)
     const bool fused = (cfg->flags & FDTD_B200_FUSED_STEP) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
                        fused_eligible(*cfg, nzl, static_cast<int>(index_bytes), cfg->nx % 4 == 0);
-    return static_cast<size_t>((fused ? 12 : 6) * sizeof(float) * plane * (nzl + 2) + plane * nzl * index_bytes + 16);
+    return static_cast<size_t>((fused ? 12 : 6) * sizeof(float) * plane * (nzl + 2) + plane * (nzl + 1) * index_bytes + 16);
 }
 
 int fdtd_b200_create_from_table(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
@@ -923,7 +930,7 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
     const uint64_t base = h->z_begin * h->plane;
     std::unordered_map<long long, uint32_t> last;
     for (uint32_t k = 0; k < n_src; ++k) {
-        if (cells[k] < base || cells[k] >= base + h->n_local) continue;
+        if (cells[k] < base || cells[k] >= base + h->n_local + (h->z_end < h->nz ? h->plane : 0)) continue;
         last[static_cast<long long>(cells[k] - base)] = k;
     }
     std::vector<std::pair<long long, uint32_t>> kept(last.begin(), last.end());
@@ -1001,7 +1008,8 @@ int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
     const int nzl = static_cast<int>(h->nzl);
     for (uint64_t s = 0; s < n_steps; ++s) {
         if (h->fused) {
-            if (int rc = launch_fused(h)) return rc;
+            if (int rc = launch_fused(h, 0, nzl)) return rc;
+            commit_fused(h);
         } else {
             if (int rc = launch_h(h, 0, nzl)) return rc;
             if (int rc = launch_e(h, 0, nzl)) return rc;
@@ -1015,20 +1023,48 @@ int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint6
     if (!h || !device_ptr) return fail(h, FDTD_B200_EINVAL, "NULL argument");
     const size_t top = static_cast<size_t>(h->plane) * (h->nzl - 1);
     const size_t above = static_cast<size_t>(h->plane) * h->nzl;
-    float* p = nullptr;
-    switch (which) {
-        case FDTD_B200_HALO_SEND_EX_TOP: p = h->f[0] + top; break;
-        case FDTD_B200_HALO_SEND_EY_TOP: p = h->f[1] + top; break;
-        case FDTD_B200_HALO_RECV_EX_LOW: p = h->alloc[0]; break;
-        case FDTD_B200_HALO_RECV_EY_LOW: p = h->alloc[1]; break;
-        case FDTD_B200_HALO_SEND_HX_BOTTOM: p = h->f[3]; break;
-        case FDTD_B200_HALO_SEND_HY_BOTTOM: p = h->f[4]; break;
-        case FDTD_B200_HALO_RECV_HX_HIGH: p = h->f[3] + above; break;
-        case FDTD_B200_HALO_RECV_HY_HIGH: p = h->f[4] + above; break;
+    const bool pending = (which & FDTD_B200_HALO_PENDING) != 0;
+    if (pending && !h->fused) return fail(h, FDTD_B200_ESTATE, "the pending buffer set exists only on fused-step handles");
+    float* const* f = pending ? h->g : h->f;              // plane 0 of each component
+    float* const* a = pending ? h->alt_alloc : h->alloc;  // the ghost plane below
+    void* p = nullptr;
+    uint64_t n = h->plane;
+    switch (which & ~FDTD_B200_HALO_PENDING) {
+        case FDTD_B200_HALO_SEND_EX_TOP: p = f[0] + top; break;
+        case FDTD_B200_HALO_SEND_EY_TOP: p = f[1] + top; break;
+        case FDTD_B200_HALO_RECV_EX_LOW: p = a[0]; break;
+        case FDTD_B200_HALO_RECV_EY_LOW: p = a[1]; break;
+        case FDTD_B200_HALO_SEND_HX_BOTTOM: p = f[3]; break;
+        case FDTD_B200_HALO_SEND_HY_BOTTOM: p = f[4]; break;
+        case FDTD_B200_HALO_RECV_HX_HIGH: p = f[3] + above; break;
+        case FDTD_B200_HALO_RECV_HY_HIGH: p = f[4] + above; break;
+        case FDTD_B200_HALO_SEND_EX_BOTTOM: p = f[0]; break;
+        case FDTD_B200_HALO_SEND_EY_BOTTOM: p = f[1]; break;
+        case FDTD_B200_HALO_SEND_EZ_BOTTOM: p = f[2]; break;
+        case FDTD_B200_HALO_RECV_EX_HIGH: p = f[0] + above; break;
+        case FDTD_B200_HALO_RECV_EY_HIGH: p = f[1] + above; break;
+        case FDTD_B200_HALO_RECV_EZ_HIGH: p = f[2] + above; break;
+        case FDTD_B200_HALO_SEND_MAT_BOTTOM: p = h->mat; n = (h->plane * h->idx_bytes + 3) / 4; break;
+        case FDTD_B200_HALO_RECV_MAT_HIGH: p = static_cast<unsigned char*>(h->mat) + above * h->idx_bytes; n = (h->plane * h->idx_bytes + 3) / 4; break;
         default: return fail(h, FDTD_B200_EINVAL, "unknown halo plane selector");
     }
     *device_ptr = p;
-    if (n_floats) *n_floats = h->plane;
+    if (n_floats) *n_floats = n;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_fused_update(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle was not created with FDTD_B200_FUSED_STEP (or the lattice is not eligible)");
+    if (z_hi > h->nzl || z_lo > z_hi) return fail(h, FDTD_B200_EINVAL, "plane range outside the slab");
+    if (int rc = set_device(h)) return rc;
+    return launch_fused(h, static_cast<int>(z_lo), static_cast<int>(z_hi));
+}
+
+int fdtd_b200_fused_commit(fdtd_b200_handle h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle was not created with FDTD_B200_FUSED_STEP (or the lattice is not eligible)");
+    commit_fused(h);
     return FDTD_B200_OK;
 }
 
@@ -1036,8 +1072,10 @@ int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle sr
     if (!dst || !src) return fail(dst, FDTD_B200_EINVAL, "NULL handle");
     if (dst->plane != src->plane) return fail(dst, FDTD_B200_EINVAL, "halo planes differ in size");
     void* pd = nullptr; void* ps = nullptr;
-    if (int rc = fdtd_b200_halo_plane(dst, which_dst, &pd, nullptr)) return rc;
-    if (int rc = fdtd_b200_halo_plane(src, which_src, &ps, nullptr)) return rc;
+    uint64_t nd = 0, ns = 0;
+    if (int rc = fdtd_b200_halo_plane(dst, which_dst, &pd, &nd)) return rc;
+    if (int rc = fdtd_b200_halo_plane(src, which_src, &ps, &ns)) return rc;
+    if (nd != ns) return fail(dst, FDTD_B200_EINVAL, "halo planes differ in size");
     // order: src stream → event → dst stream
     cudaEvent_t ev;
     CU_TRY(src, cudaSetDevice(src->device));
@@ -1045,7 +1083,7 @@ int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle sr
     CU_TRY(src, cudaEventRecord(ev, src->stream));
     CU_TRY(dst, cudaSetDevice(dst->device));
     CU_TRY(dst, cudaStreamWaitEvent(dst->stream, ev, 0));
-    const size_t bytes = static_cast<size_t>(dst->plane) * sizeof(float);
+    const size_t bytes = static_cast<size_t>(nd) * sizeof(float);
     if (dst->device == src->device) CU_TRY(dst, cudaMemcpyAsync(pd, ps, bytes, cudaMemcpyDeviceToDevice, dst->stream));
     else CU_TRY(dst, cudaMemcpyPeerAsync(pd, dst->device, ps, src->device, bytes, dst->stream));
     // the source plane must not be overwritten before the copy has run: src waits for it

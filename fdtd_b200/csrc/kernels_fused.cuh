@@ -22,7 +22,8 @@
 
 namespace fdtd_b200 {
 
-// Tensor maps of the step's input arrays (3-D: x, y, z; boxes of one plane of a CTA tile incl. halos).
+// Tensor maps of the step's input arrays (3-D: x, y, z; boxes of one plane of a CTA tile incl. halos).  The field maps
+// start at the lower ghost plane (z index = plane + 1) so that slab handles can fetch their neighbours' planes.
 struct FusedMaps {
     CUtensorMap e[3];   // old Ex, Ey, Ez : box (PE, E_ROWS, 1)
     CUtensorMap h[3];   // old Hx, Hy, Hz : box (PE, H_ROWS, 1)
@@ -42,7 +43,9 @@ struct FusedView {
     const void* mat;
     const float4* table;
     int n_table, table_in_smem;
-    int nx, ny, nz;
+    int nx, ny, nz;       // nz = planes owned by this handle (z-slab)
+    int z_lo, z_hi;       // planes updated by this launch
+    int lo_open, hi_open; // a neighbouring slab exists below / above: ghost planes -1 / nz hold its old fields
     float dx[3], inv_dx[3];
 };
 
@@ -101,8 +104,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
 
     const int x0 = blockIdx.x * (4 * BX);
     const int y0 = blockIdx.y * LO::CORE_ROWS;
-    const int za = blockIdx.z * zc;
-    const int zb = min(za + zc, V.nz);
+    const int za = V.z_lo + blockIdx.z * zc;
+    const int zb = min(za + zc, V.z_hi);
     const int n = zb - za;
     const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
     // forcing may hit the recomputed halo as well: test the extended box
@@ -114,7 +117,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const size_t sy = static_cast<size_t>(V.nx);
     const size_t sz = sy * static_cast<size_t>(V.ny);
     const bool right = x0 + 4 * BX < V.nx;
-    const int last_h_plane = (zb < V.nz) ? zb : zb - 1;            // H'/old-E planes za..last_h_plane are needed
+    const bool below = (za > 0) || (V.lo_open != 0);                // old-E plane za-1 exists (own plane or ghost)
+    const int last_h_plane = (zb < V.nz || V.hi_open != 0) ? zb : zb - 1;   // H'/old-E planes za..last_h_plane are needed
     const int n_h = last_h_plane - za + 1;                          // number of H-plane iterations with a phase A
 
     // ---- producer: one lane of the last warp issues 7 tensor copies per plane ------------------------------------
@@ -124,7 +128,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             mbar_arrive_expect_tx(bar, 3u * LO::E_BOX_BYTES);
             float* s = reinterpret_cast<float*>(e_slots + static_cast<size_t>(slot) * LO::E_SLOT_BYTES);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * E_COMP, &M.e[c], x0 - 4, y0 - 1, plane, bar);
+            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * E_COMP, &M.e[c], x0 - 4, y0 - 1, plane + 1, bar);
         }
     };
     auto issue_h = [&](int plane, int slot) {
@@ -134,14 +138,14 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             unsigned char* sl = h_slots + static_cast<size_t>(slot) * LO::H_SLOT_BYTES;
             float* s = reinterpret_cast<float*>(sl);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * H_COMP, &M.h[c], x0 - 4, y0, plane, bar);
+            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * H_COMP, &M.h[c], x0 - 4, y0, plane + 1, bar);
             tma_load_3d(sl + 3 * H_COMP * 4, &M.mat, x0, y0, plane, bar);
         }
     };
     // E ring index of plane z: e = z - (za - 1); H ring index: k = z - za
     const bool producer = tid >= NT - 32;                           // the last warp: it has no E' work (top thread row)
     if (producer) {
-        if (za > 0) issue_e(za - 1, 0);
+        if (below) issue_e(za - 1, 0);
         else if (lane == 0) mbar_arrive_expect_tx(fullE + 0, 0u);   // keep slot 0's phase sequence uniform (phase 0 completes empty)
         issue_e(za, 1);
         if (n_h > 1) issue_e(za + 1, 2);
@@ -167,14 +171,14 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             const int e_idx = k + 1;
             mbar_wait(fullE + (e_idx % LO::NE), static_cast<uint32_t>((e_idx / LO::NE) & 1));
             mbar_wait(fullH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
-            if (k == 0 && za > 0) mbar_wait(fullE + 0, 0u);
+            if (k == 0 && below) mbar_wait(fullE + 0, 0u);
             e_cur = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(e_idx % LO::NE) * LO::E_SLOT_BYTES);
             const float* e_low = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES);
             const unsigned char* hsl = h_slots + static_cast<size_t>(k % LO::NH) * LO::H_SLOT_BYTES;
             const float* h_old = reinterpret_cast<const float*>(hsl);
             const IdxT* s_mat = reinterpret_cast<const IdxT*>(hsl + 3 * H_COMP * 4);
             float* hb_w = hb + static_cast<size_t>(k & 1) * 3 * H_COMP;
-            const bool z_in = zk > 0;
+            const bool z_in = (zk > 0) || (V.lo_open != 0);
 
             // ---- phase A: H'(z_k) on the CTA's BY rows -----------------------------------------------------------
             {

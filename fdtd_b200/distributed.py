@@ -78,6 +78,19 @@ class CudaSlabEngine:
             "send_h_bottom": planes(L.HALO_SEND_HX_BOTTOM, L.HALO_SEND_HY_BOTTOM),
             "recv_h_high": planes(L.HALO_RECV_HX_HIGH, L.HALO_RECV_HY_HIGH),
         }
+        # fused-step handles: the buffer sets alternate, so planes are looked up per call (tensors cached by address)
+        self.fused = bool(state.uses_fused)
+        self._dev = dev
+        self._by_ptr = {}
+        self._fused_names = {
+            "send_up": (L.HALO_SEND_EX_TOP, L.HALO_SEND_EY_TOP),
+            "recv_low": (L.HALO_RECV_EX_LOW, L.HALO_RECV_EY_LOW),
+            "send_down": (L.HALO_SEND_EX_BOTTOM, L.HALO_SEND_EY_BOTTOM, L.HALO_SEND_EZ_BOTTOM, L.HALO_SEND_HX_BOTTOM, L.HALO_SEND_HY_BOTTOM),
+            "recv_high": (L.HALO_RECV_EX_HIGH, L.HALO_RECV_EY_HIGH, L.HALO_RECV_EZ_HIGH, L.HALO_RECV_HX_HIGH, L.HALO_RECV_HY_HIGH),
+            "send_mat_bottom": (L.HALO_SEND_MAT_BOTTOM,),
+            "recv_mat_high": (L.HALO_RECV_MAT_HIGH,),
+        }
+        self._pending_bit = L.HALO_PENDING
 
     def update_h(self, z_lo: int, z_hi: int) -> None:
         self.state.update_h(z_lo, z_hi)
@@ -88,8 +101,24 @@ class CudaSlabEngine:
     def end_step(self) -> None:
         self.state.end_step()
 
-    def halo(self, name: str):
-        return self._halo[name]
+    def halo(self, name: str, pending: bool = False):
+        if name in self._halo:
+            return self._halo[name]
+        out = []
+        for which in self._fused_names[name]:
+            ptr, n = self.state.halo_plane(which | (self._pending_bit if pending else 0))
+            t = self._by_ptr.get((ptr, n))
+            if t is None:
+                t = self._torch.as_tensor(CudaHaloView(ptr, n), device=self._dev)
+                self._by_ptr[(ptr, n)] = t
+            out.append(t)
+        return out
+
+    def fused_update(self, z_lo: int, z_hi: int) -> None:
+        self.state.fused_update(z_lo, z_hi)
+
+    def fused_commit(self) -> None:
+        self.state.fused_commit()
 
 
 class SlabStepper:
@@ -100,18 +129,21 @@ class SlabStepper:
         self.lower: Optional[int] = rank - 1 if rank > 0 else None
         self.upper: Optional[int] = rank + 1 if rank + 1 < world else None
         self.exchanges = 0
+        self.fused = bool(getattr(engine, "fused", False))
+        if self.fused:
+            self._setup_fused()
 
     # -- transport -----------------------------------------------------------------------------
-    def _start(self, send_name: str, send_to: Optional[int], recv_name: str, recv_from: Optional[int]):
+    def _start(self, send_name: str, send_to: Optional[int], recv_name: str, recv_from: Optional[int], **kw):
         import torch.distributed as dist
 
         ops = []
         # post receives first, lowest peer first on every rank → the pairing is deadlock-free for any backend
         if recv_from is not None:
-            for t in self.engine.halo(recv_name):
+            for t in self.engine.halo(recv_name, **kw):
                 ops.append(dist.P2POp(dist.irecv, t, recv_from, self.group))
         if send_to is not None:
-            for t in self.engine.halo(send_name):
+            for t in self.engine.halo(send_name, **kw):
                 ops.append(dist.P2POp(dist.isend, t, send_to, self.group))
         if not ops:
             return []
@@ -133,13 +165,51 @@ class SlabStepper:
 
     def refresh_halos(self) -> None:
         """Make ghost planes consistent after fields were written from outside (write_field)."""
+        if self.fused:
+            self._finish(self._start_fused_exchange(pending=False))
+            return
         self._finish(self.start_h_exchange())
         self._finish(self.start_e_exchange())
+
+    # -- fused single-pass step: one exchange per step ---------------------------------------------
+    def _setup_fused(self) -> None:
+        """The fused kernel recomputes H' of the upper neighbour's first plane, so it needs that plane's material
+        index (static, shipped once) besides its old E and Hx,Hy (shipped every step)."""
+        self._finish(self._start("send_mat_bottom", self.lower, "recv_mat_high", self.upper))
+
+    def _start_fused_exchange(self, pending: bool):
+        """top Ex,Ey go UP (the upper rank's d/dz of its first plane); the whole first plane's E and Hx,Hy go DOWN
+        (the lower rank recomputes H' there for its top plane's E')."""
+        works = self._start("send_up", self.upper, "recv_low", self.lower, pending=pending)
+        works += self._start("send_down", self.lower, "recv_high", self.upper, pending=pending)
+        return works
+
+    def _step_fused(self) -> None:
+        e, n = self.engine, self.engine.n_planes
+        lo = 1 if (self.lower is not None and self.overlap and n >= 3) else 0
+        hi = n - 1 if (self.upper is not None and self.overlap and n >= 3) else n
+        # boundary planes first (they are what the neighbours wait for), written into the pending buffer set
+        if hi < n:
+            e.fused_update(hi, n)
+        if lo > 0:
+            e.fused_update(0, lo)
+        if lo > 0 or hi < n:
+            works = self._start_fused_exchange(pending=True)   # overlaps the interior update below
+            e.fused_update(lo, hi)
+        else:
+            e.fused_update(0, n)
+            works = self._start_fused_exchange(pending=True)
+        self._finish(works)
+        e.fused_commit()
+        e.end_step()
 
     # -- stepping ------------------------------------------------------------------------------
     def step(self, n_steps: int = 1) -> None:
         e, n = self.engine, self.engine.n_planes
         for _ in range(n_steps):
+            if self.fused:
+                self._step_fused()
+                continue
             if self.overlap and n > 1:
                 # H: the bottom plane feeds the lower rank — do it first, ship it, then the rest
                 e.update_h(0, 1)

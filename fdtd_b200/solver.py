@@ -336,6 +336,12 @@ class FdtdB200SolverState:
     def update_e(self, z_lo: int, z_hi: int) -> None:
         L.check(self._lib.fdtd_b200_update_e(self._h, z_lo, z_hi), self._h)
 
+    def fused_update(self, z_lo: int, z_hi: int) -> None:
+        L.check(self._lib.fdtd_b200_fused_update(self._h, z_lo, z_hi), self._h)
+
+    def fused_commit(self) -> None:
+        L.check(self._lib.fdtd_b200_fused_commit(self._h), self._h)
+
     def end_step(self) -> None:
         L.check(self._lib.fdtd_b200_end_step(self._h), self._h)
 

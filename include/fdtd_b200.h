@@ -208,6 +208,11 @@ int fdtd_b200_update_h(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
 int fdtd_b200_update_e(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
 /* tick += 1, time += dt, consume one forcing row, advance the probe ring. */
 int fdtd_b200_end_step(fdtd_b200_handle h);
+/* Fused-step handles (FDTD_B200_FUSED_STEP): update planes [z_lo, z_hi) with the single-pass kernel, reading the current
+ * buffer set (incl. ghost planes) and writing the pending one; launches of disjoint ranges are independent.  commit
+ * makes the pending set current (call once per step after every plane was updated, then fdtd_b200_end_step). */
+int fdtd_b200_fused_update(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
+int fdtd_b200_fused_commit(fdtd_b200_handle h);
 
 /* Halo planes (device pointers, nx*ny floats each).  which: */
 enum {
@@ -218,7 +223,20 @@ enum {
     FDTD_B200_HALO_SEND_HX_BOTTOM = 4, /* first owned plane of Hx — goes down after the H half-step */
     FDTD_B200_HALO_SEND_HY_BOTTOM = 5,
     FDTD_B200_HALO_RECV_HX_HIGH = 6, /* ghost plane above the last plane */
-    FDTD_B200_HALO_RECV_HY_HIGH = 7
+    FDTD_B200_HALO_RECV_HY_HIGH = 7,
+    /* fused-step slabs additionally ship their whole first plane down (the lower rank recomputes H' of it): */
+    FDTD_B200_HALO_SEND_EX_BOTTOM = 8,
+    FDTD_B200_HALO_SEND_EY_BOTTOM = 9,
+    FDTD_B200_HALO_SEND_EZ_BOTTOM = 10,
+    FDTD_B200_HALO_RECV_EX_HIGH = 11,
+    FDTD_B200_HALO_RECV_EY_HIGH = 12,
+    FDTD_B200_HALO_RECV_EZ_HIGH = 13,
+    /* material index of the first owned plane / of the plane above the slab (exchanged once; n_floats = bytes/4) */
+    FDTD_B200_HALO_SEND_MAT_BOTTOM = 14,
+    FDTD_B200_HALO_RECV_MAT_HIGH = 15,
+    /* OR-ed into a selector: the plane of the PENDING buffer set of a fused-step handle (what fdtd_b200_fused_update
+       is writing and fdtd_b200_fused_commit will make current) */
+    FDTD_B200_HALO_PENDING = 0x100
 };
 int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint64_t* n_floats);
 /* Single-process multi-GPU transport: copy halo plane `which_src` of `src` into `which_dst` of `dst`

@@ -110,11 +110,12 @@ def test_memory_required(b200):
     be = b200.FdtdB200Backend()
     need = be.memory_required(cfg)
     cells = 512 ** 3
-    assert need == 24 * 512 * 512 * 514 + cells + 16
+    assert need == 24 * 512 * 512 * 514 + cells + 512 * 512 + 16      # fields (+2 ghost planes) + u8 index (+1 plane)
     assert need / cells < 26                      # vs 136 B/cell (cpu/mod.rs:217-221) and 80 B/cell (wgpu/mod.rs:129-133)
-    assert be.memory_required(cfg, 2) == need + cells
+    assert be.memory_required(cfg, 2) == need + cells + 512 * 512
+    assert b200.FdtdB200Backend(fused_step=True).memory_required(cfg) == need + 24 * 512 * 512 * 514   # ping-pong set
     slab = b200.FdtdB200Backend(z_slab=(128, 256))
-    assert slab.memory_required(cfg) == 24 * 512 * 512 * 130 + 512 * 512 * 128 + 16
+    assert slab.memory_required(cfg) == 24 * 512 * 512 * 130 + 512 * 512 * 129 + 16
 
 
 def test_invalid_configs_are_rejected_without_a_device(b200):

@@ -100,3 +100,57 @@ def test_fused_u16_index_and_fallbacks(b200, oracle, tune):
     w2 = _random_workload(b200, (36, 5, 4), seed=2)
     st2, _ = run(b200, w2, 2, exact=True, fused=True)
     assert not st2.uses_fused and st2.tick() == 2
+
+
+@pytest.mark.parametrize("size,cut,ranges", [((128, 9, 10), 6, "whole"), ((256, 5, 9), 4, "split"), ((128, 8, 5), 1, "whole")])
+def test_fused_two_slabs_equal_one_domain(b200, tune, size, cut, ranges):
+    """Two fused-step z-slab handles on one GPU, halos moved with fdtd_b200_halo_copy (the protocol distributed.py
+    runs over NCCL): bit-identical to the whole-domain run, with sources and probes next to the cut."""
+    from fdtd_b200 import _lib as L
+
+    tune(None)
+    w = _random_workload(b200, size, seed=41)
+    nz = size[2]
+    w.sources = [((size[0] // 2, size[1] // 2, cut), w.sources[0][1]), ((5, 1, cut - 1), b200.GaussianPulse(0.2, 0.5).with_amplitudes((1, 2, 3), (-1, 0.5, 2)))]
+    probes = [(size[0] // 2, size[1] // 2, cut - 1), (3, 2, cut), (size[0] - 1, size[1] - 1, nz - 1)]
+    init = random_fields(w, seed=14)
+    steps = 5
+    whole, s_whole = run(b200, w, steps, exact=True, fused=True, init=init, probes=probes)
+    tab = w.source_table(steps)
+    slabs = []
+    for a, b in ((0, cut), (cut, nz)):
+        be = b200.FdtdB200Backend(exact_arithmetic=True, fused_step=True, z_slab=(a, b))
+        st = be.create_instance(w.solver_config(), w.domain()).create_state()
+        assert st.uses_fused
+        st.write_field(b200.FieldComponent.E, init[0][a:b], (0, 0, a), (size[0], size[1], b))
+        st.write_field(b200.FieldComponent.H, init[1][a:b], (0, 0, a), (size[0], size[1], b))
+        st.register_probes(probes)
+        st.set_source_table(w.source_points(), tab)
+        slabs.append(st)
+    lo, hi = slabs
+    lib = b200.lib()
+
+    def exchange(pending):
+        p = L.HALO_PENDING if pending else 0
+        for d, s in ((L.HALO_RECV_EX_LOW, L.HALO_SEND_EX_TOP), (L.HALO_RECV_EY_LOW, L.HALO_SEND_EY_TOP)):
+            L.check(lib.fdtd_b200_halo_copy(hi._h, d | p, lo._h, s | p))
+        for d, s in ((L.HALO_RECV_EX_HIGH, L.HALO_SEND_EX_BOTTOM), (L.HALO_RECV_EY_HIGH, L.HALO_SEND_EY_BOTTOM), (L.HALO_RECV_EZ_HIGH, L.HALO_SEND_EZ_BOTTOM),
+                     (L.HALO_RECV_HX_HIGH, L.HALO_SEND_HX_BOTTOM), (L.HALO_RECV_HY_HIGH, L.HALO_SEND_HY_BOTTOM)):
+            L.check(lib.fdtd_b200_halo_copy(lo._h, d | p, hi._h, s | p))
+
+    L.check(lib.fdtd_b200_halo_copy(lo._h, L.HALO_RECV_MAT_HIGH, hi._h, L.HALO_SEND_MAT_BOTTOM))
+    exchange(False)
+    for _ in range(steps):
+        if ranges == "split" and cut >= 3:
+            lo.fused_update(cut - 1, cut); hi.fused_update(0, 1)
+            exchange(True)
+            lo.fused_update(0, cut - 1); hi.fused_update(1, nz - cut)
+        else:
+            lo.fused_update(0, cut); hi.fused_update(0, nz - cut)
+            exchange(True)
+        for st in slabs:
+            st.fused_commit(); st.end_step()
+    for comp in (b200.FieldComponent.E, b200.FieldComponent.H):
+        got = np.concatenate([lo.read_field(comp), hi.read_field(comp)], axis=0)
+        assert np.array_equal(got, whole.read_field(comp))
+    assert np.array_equal(lo.read_probes(0, steps) + hi.read_probes(0, steps), s_whole)

@@ -21,6 +21,7 @@ def main():
     lattice = tuple(int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "64,48,40").split(","))
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 25
     overlap = (sys.argv[3] != "0") if len(sys.argv) > 3 else True
+    fused = (sys.argv[4] != "0") if len(sys.argv) > 4 else False
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     zb, ze = partition_z(lattice[2], world)[rank]
@@ -31,7 +32,7 @@ def main():
     w.sources = [(src_pt, w.sources[0][1])]
     w.probes = [(lattice[0] // 2 + 3, lattice[1] // 2, cut), (lattice[0] // 2, lattice[1] // 2 + 2, cut - 1), (1, 1, lattice[2] - 1)]
     tab = w.source_table(steps)
-    be = fdtd_b200.FdtdB200Backend(device=local, z_slab=(zb, ze))
+    be = fdtd_b200.FdtdB200Backend(device=local, z_slab=(zb, ze), fused_step=fused)
     st = be.create_instance(w.solver_config(), w.domain()).create_state()
     st.register_probes(w.probes)
     st.set_source_table(w.source_points(), tab)
@@ -60,7 +61,7 @@ def main():
         eg, hg = torch.cat(es).cpu().numpy(), torch.cat(hs).cpu().numpy()
         ok = np.array_equal(eg, ef) and np.array_equal(hg, hf) and np.array_equal(pr.cpu().numpy(), full.read_probes(0, steps))
         ok = ok and bool(np.any(ef)) and st.tick() == steps
-        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
+        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} fused={st.uses_fused} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
