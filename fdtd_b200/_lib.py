@@ -47,6 +47,13 @@ class Source(C.Structure):
     _fields_ = [("cell", C.c_uint64), ("j", C.c_float * 3), ("m", C.c_float * 3)]
 
 
+class Shape(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("label", C.c_uint32), ("params", C.c_float * 3), ("rot", C.c_float * 9),
+                ("translation", C.c_float * 3), ("reserved", C.c_float)]
+
+
+SHAPE_BALL, SHAPE_CUBOID, SHAPE_CYLINDER = 0, 1, 2
+
 # every symbol include/fdtd_b200.h declares: name -> (restype, argtypes)
 _H = C.c_void_p
 _u64p = C.POINTER(C.c_uint64)
@@ -91,6 +98,8 @@ SYMBOLS = {
     "fdtd_b200_fused_commit": (C.c_int, [_H]),
     "fdtd_b200_halo_plane": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p), _u64p]),
     "fdtd_b200_halo_copy": (C.c_int, [_H, C.c_int, _H, C.c_int]),
+    "fdtd_b200_rasterize_scene": (C.c_int, [C.c_int, _u64p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32, _u32p]),
+    "fdtd_b200_set_materials_from_scene": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32]),
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_write_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_device_field": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p)]),

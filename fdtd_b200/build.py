@@ -1,6 +1,7 @@
 """Builds fdtd_b200/libfdtd_b200.so (CUDA, sm_100a) in-tree with nvcc.  No torch involved."""
 from __future__ import annotations
 
+import glob
 import os
 import shutil
 import subprocess
@@ -8,10 +9,7 @@ import subprocess
 _DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_DIR, "libfdtd_b200.so")
 _SOURCES = [os.path.join(_DIR, "csrc", "fdtd_b200.cu")]
-_DEPS = _SOURCES + [
-    os.path.join(_DIR, "csrc", "kernels.cuh"),
-    os.path.join(os.path.dirname(_DIR), "include", "fdtd_b200.h"),
-]
+_DEPS = _SOURCES + sorted(glob.glob(os.path.join(_DIR, "csrc", "*.cuh"))) + [os.path.join(os.path.dirname(_DIR), "include", "fdtd_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -25,12 +25,13 @@ class Workload:
     sources: list                       # [(point, WithAmplitudes)]
     probes: list = field(default_factory=list)   # [point]
     steps: int = 0
+    scene: Optional[object] = None      # scene.SceneDomain: the lattice is rasterised on the device (then `ids` is None)
 
     def solver_config(self) -> FdtdSolverConfig:
         return FdtdSolverConfig.from_lattice(self.lattice, self.resolution, self.constants)
 
-    def domain(self) -> MaterialLattice:
-        return MaterialLattice(self.palette, self.ids)
+    def domain(self):
+        return self.scene if self.scene is not None else MaterialLattice(self.palette, self.ids)
 
     @property
     def n_cells(self) -> int:
@@ -237,3 +238,45 @@ def heterogeneous_slab_labels(lattice: tuple, z_begin: int, z_end: int, n_balls:
         c[2] -= z_begin  # slab-local z
         _ball_mask_apply(labels, free, c, radii[b], 1 + depth + (b % 4))
     return labels.reshape(-1)
+
+
+# ---- config 5: dipole antenna from a NEC deck -------------------------------------------------------------
+NEC_DIPOLE_DECK = """CM half-wave dipole
+CE
+GW 1 21 0 0 -0.25 0 0 0.25 0.005
+GE 0
+EX 0 1 11 0 1 0
+RP 0 19 1 1000 0 0 5 0
+EN
+"""
+
+
+def config5_nec_dipole(n: int = 256, steps: int = 2000, deck: str = NEC_DIPOLE_DECK) -> Workload:
+    """The deck goes through the NEC parser/interpreter (nec.py) and becomes 21 Y-aligned cylinders exactly as the
+    application lays them out (composer/file_formats/nec.rs:47-70 — strung along +Y from the wire's first end whatever the
+    wire's direction); wire segments are σ = 1e4 conductor except the centre segment, which stays vacuum and holds the feed:
+    a Gaussian j_y at its centre cell.  The lattice is centred on the wire, dx = wire length / (63·n/256) so the wire spans
+    a quarter of it; "far-field" probes = 16 cells on a circle of radius 100·n/256 in the xz-plane + 2 on the wire axis (the
+    reference has no near-to-far-field transform and reads no EX/RP cards, nec-file/src/parser.rs:91-100)."""
+    from .nec import NecFile, wire_cylinders
+    from .scene import CoordinateTransformations, SceneDomain, Shape
+
+    cyl = wire_cylinders(NecFile.from_text(deck))
+    length = float(sum(2.0 * float(c.half_height) for c in cyl))
+    s = n / 256.0
+    dx = length / (63.0 * s)
+    res = Resolution((dx, dx, dx), 0.25 * dx)
+    mid = cyl[len(cyl) // 2]
+    c = n // 2
+    mins = tuple(float(mid.centre[a]) - c * dx for a in range(3))
+    tf = CoordinateTransformations.for_fdtd(res, (n, n, n), aabb_mins=mins)
+    wire = Material(eletrical_conductivity=1.0e4)
+    shapes = [Shape.cylinder(float(k.half_height), float(k.radius), Material.VACUUM if k is mid else wire,
+                             tuple(float(v) for v in k.centre)) for k in cyl]
+    scene = SceneDomain(shapes, tf, Material.VACUUM)
+    src = GaussianPulse(50 * res.temporal, 10 * res.temporal).with_amplitudes((0.0, 50.0, 0.0), (0.0, 0.0, 0.0))
+    r = int(round(100 * s))
+    probes = [(c + int(round(r * np.cos(2 * np.pi * k / 16))), c, c + int(round(r * np.sin(2 * np.pi * k / 16)))) for k in range(16)]
+    probes += [(c, c + r, c), (c, c - r, c)]
+    return Workload(f"nec_dipole{n}", (n, n, n), res, PhysicalConstants.REDUCED, scene.palette, None, [((c, c, c), src)], probes, steps,
+                    scene=scene)

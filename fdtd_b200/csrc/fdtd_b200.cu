@@ -16,6 +16,7 @@
 #include "kernels.cuh"
 #include "kernels_bulk.cuh"
 #include "kernels_fused.cuh"
+#include "kernels_scene.cuh"
 
 using namespace fdtd_b200;
 
@@ -1251,6 +1252,165 @@ int fdtd_b200_project(fdtd_b200_handle h, int component, const float projection[
         CU_TRY(h, cudaMemcpyAsync(out_rgba, d_out, bytes, cudaMemcpyDeviceToHost, h->stream));
         CU_TRY(h, cudaStreamSynchronize(h->stream));
     }
+    return FDTD_B200_OK;
+}
+
+}  // extern "C"
+
+// ---- scene → material lattice (kernels_scene.cuh) --------------------------------------------------------------------
+namespace {
+
+static_assert(sizeof(fdtd_b200_shape) == sizeof(SceneShape), "fdtd_b200_shape mirrors SceneShape");
+
+// Conservative lattice-space bounds of every shape: its bounding sphere pushed through the inverse affine map, padded.
+void scene_boxes(const double m[16], const uint64_t dims[3], const fdtd_b200_shape* shapes, uint32_t n, std::vector<SceneBox>* out) {
+    const double a[3][3] = {{m[0], m[1], m[2]}, {m[4], m[5], m[6]}, {m[8], m[9], m[10]}};
+    const double det = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) - a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) +
+                       a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+    const bool invertible = std::isfinite(det) && std::fabs(det) > 1e-300;
+    double inv[3][3] = {};
+    if (invertible) {
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) {
+                const int r1 = (c + 1) % 3, r2 = (c + 2) % 3, c1 = (r + 1) % 3, c2 = (r + 2) % 3;
+                inv[r][c] = (a[r1][c1] * a[r2][c2] - a[r1][c2] * a[r2][c1]) / det;   // adjugate (cyclic cofactors)
+            }
+    }
+    out->resize(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        SceneBox b;
+        for (int ax = 0; ax < 3; ++ax) { b.lo[ax] = 0; b.hi[ax] = static_cast<int>(dims[ax]); }
+        const fdtd_b200_shape& sh = shapes[i];
+        double radius = 0.0;
+        if (sh.kind == FDTD_B200_SHAPE_BALL) radius = std::fabs(sh.params[0]);
+        else if (sh.kind == FDTD_B200_SHAPE_CUBOID) radius = std::sqrt(double(sh.params[0]) * sh.params[0] + double(sh.params[1]) * sh.params[1] + double(sh.params[2]) * sh.params[2]);
+        else radius = std::sqrt(double(sh.params[0]) * sh.params[0] + double(sh.params[1]) * sh.params[1]);
+        if (invertible && std::isfinite(radius)) {
+            const double d[3] = {sh.translation[0] - m[3], sh.translation[1] - m[7], sh.translation[2] - m[11]};
+            for (int ax = 0; ax < 3; ++ax) {
+                const double c = inv[ax][0] * d[0] + inv[ax][1] * d[1] + inv[ax][2] * d[2];
+                const double ext = radius * std::sqrt(inv[ax][0] * inv[ax][0] + inv[ax][1] * inv[ax][1] + inv[ax][2] * inv[ax][2]);
+                const double pad = 2.0 + 1e-4 * (std::fabs(c) + ext);      // f32 rounding of world points and of the test itself
+                const double lo = std::floor(c - ext - pad), hi = std::ceil(c + ext + pad) + 1.0;
+                if (std::isfinite(lo) && std::isfinite(hi)) {
+                    b.lo[ax] = static_cast<int>(std::min(std::max(lo, 0.0), double(dims[ax])));
+                    b.hi[ax] = static_cast<int>(std::min(std::max(hi, 0.0), double(dims[ax])));
+                }
+            }
+        }
+        (*out)[i] = b;
+    }
+}
+
+struct SceneDevice {
+    SceneShape* shapes = nullptr;
+    SceneBox* boxes = nullptr;
+    ~SceneDevice() { cudaFree(shapes); cudaFree(boxes); }
+};
+
+int scene_validate(const uint64_t dims[3], const double m[16], const fdtd_b200_shape* shapes, uint32_t n, std::string* why) {
+    if (!dims || !m) { *why = "NULL argument"; return FDTD_B200_EINVAL; }
+    if (n && !shapes) { *why = "shapes is NULL"; return FDTD_B200_EINVAL; }
+    if (n > 1024) { *why = "at most 1024 shapes per scene (they are staged in shared memory)"; return FDTD_B200_EINVAL; }
+    for (int i = 0; i < 12; ++i) if (!std::isfinite(m[i])) { *why = "solver_to_world is not finite"; return FDTD_B200_EINVAL; }
+    if (m[12] != 0.0 || m[13] != 0.0 || m[14] != 0.0 || m[15] != 1.0) { *why = "solver_to_world must be affine (last row 0 0 0 1)"; return FDTD_B200_EINVAL; }
+    for (uint32_t i = 0; i < n; ++i) if (shapes[i].kind > FDTD_B200_SHAPE_CYLINDER) { *why = "unknown shape kind"; return FDTD_B200_EINVAL; }
+    return FDTD_B200_OK;
+}
+
+int scene_upload(fdtd_b200_handle h, const uint64_t dims[3], const double m[16], const fdtd_b200_shape* shapes, uint32_t n, cudaStream_t st,
+                 SceneDevice* dev, SceneView* V) {
+    std::vector<SceneBox> boxes;
+    scene_boxes(m, dims, shapes, n, &boxes);
+    if (n) {
+        CU_TRY(h, cudaMalloc(&dev->shapes, n * sizeof(SceneShape)));
+        CU_TRY(h, cudaMalloc(&dev->boxes, n * sizeof(SceneBox)));
+        CU_TRY(h, cudaMemcpyAsync(dev->shapes, shapes, n * sizeof(SceneShape), cudaMemcpyHostToDevice, st));
+        CU_TRY(h, cudaMemcpyAsync(dev->boxes, boxes.data(), n * sizeof(SceneBox), cudaMemcpyHostToDevice, st));
+        CU_TRY(h, cudaStreamSynchronize(st));   // `boxes` is a local
+    }
+    for (int i = 0; i < 12; ++i) V->m[i] = m[i];
+    V->shapes = dev->shapes; V->boxes = dev->boxes; V->n_shapes = static_cast<int>(n);
+    V->nx = static_cast<int>(dims[0]); V->ny = static_cast<int>(dims[1]);
+    return FDTD_B200_OK;
+}
+
+template <typename OutT>
+int scene_launch(fdtd_b200_handle h, const SceneView& V, OutT* out, cudaStream_t st) {
+    const long long quads = static_cast<long long>((V.nx + 3) / 4) * V.ny * V.n_planes;
+    if (quads <= 0) return FDTD_B200_OK;
+    const int blocks = static_cast<int>(std::min<long long>((quads + 255) / 256, 148LL * 32));
+    const size_t smem = static_cast<size_t>(V.n_shapes) * (sizeof(SceneShape) + sizeof(SceneBox));
+    auto k = k_rasterize_scene<OutT>;
+    if (smem > 48 * 1024) CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    k<<<blocks, 256, smem, st>>>(V, out);
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fdtd_b200_rasterize_scene(int device, const uint64_t dims[3], uint64_t z_begin, uint64_t z_end, const double solver_to_world[16],
+                              const fdtd_b200_shape* shapes, uint32_t n_shapes, uint32_t default_label, uint32_t* ids_out) {
+    std::string why;
+    if (int rc = scene_validate(dims, solver_to_world, shapes, n_shapes, &why)) return fail(nullptr, rc, why);
+    if (!ids_out) return fail(nullptr, FDTD_B200_EINVAL, "ids_out is NULL");
+    if (dims[0] == 0 || dims[1] == 0 || dims[2] == 0 || dims[0] > 0x7fffffffull || dims[1] > 0x7fffffffull || dims[2] > 0x7fffffffull)
+        return fail(nullptr, FDTD_B200_EINVAL, "lattice dimensions out of range");
+    if (z_begin >= z_end || z_end > dims[2]) return fail(nullptr, FDTD_B200_EINVAL, "plane range [z_begin, z_end) is empty or outside the lattice");
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+        (void)cudaGetLastError();
+        return fail(nullptr, FDTD_B200_ECUDA, "no CUDA device available: fdtd_b200 has no CPU fallback");
+    }
+    if (device < 0 || device >= n_dev) return fail(nullptr, FDTD_B200_EINVAL, "device ordinal out of range");
+    CU_TRY(nullptr, cudaSetDevice(device));
+    SceneDevice dev;
+    SceneView V{};
+    if (int rc = scene_upload(nullptr, dims, solver_to_world, shapes, n_shapes, nullptr, &dev, &V)) return rc;
+    V.default_label = default_label;
+    const uint64_t plane = dims[0] * dims[1];
+    const uint64_t chunk_planes = std::max<uint64_t>(1, std::min<uint64_t>(z_end - z_begin, (uint64_t(1) << 26) / plane));  // ≤ 256 MB staging
+    uint32_t* d_out = nullptr;
+    CU_TRY(nullptr, cudaMalloc(&d_out, chunk_planes * plane * sizeof(uint32_t)));
+    int rc = FDTD_B200_OK;
+    for (uint64_t z = z_begin; z < z_end && rc == FDTD_B200_OK; z += chunk_planes) {
+        const uint64_t np = std::min(chunk_planes, z_end - z);
+        V.z0 = static_cast<long long>(z); V.n_planes = static_cast<long long>(np);
+        rc = scene_launch<uint32_t>(nullptr, V, d_out, nullptr);
+        if (rc == FDTD_B200_OK) {
+            const cudaError_t e = cudaMemcpy(ids_out + (z - z_begin) * plane, d_out, np * plane * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) { (void)cudaGetLastError(); rc = fail(nullptr, FDTD_B200_ECUDA, std::string("rasterize readback: ") + cudaGetErrorString(e)); }
+        }
+    }
+    cudaFree(d_out);
+    return rc;
+}
+
+int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_to_world[16], const fdtd_b200_shape* shapes,
+                                       uint32_t n_shapes, uint32_t default_label) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "handle is NULL");
+    const uint64_t dims[3] = {h->nx, h->ny, h->nz};
+    std::string why;
+    if (int rc = scene_validate(dims, solver_to_world, shapes, n_shapes, &why)) return fail(h, rc, why);
+    if (default_label >= h->n_table) return fail(h, FDTD_B200_EINVAL, "default label out of range of the palette/table");
+    for (uint32_t i = 0; i < n_shapes; ++i)
+        if (shapes[i].label >= h->n_table) return fail(h, FDTD_B200_EINVAL, "shape label out of range of the palette/table");
+    CU_TRY(h, cudaSetDevice(h->device));
+    SceneDevice dev;
+    SceneView V{};
+    if (int rc = scene_upload(h, dims, solver_to_world, shapes, n_shapes, h->stream, &dev, &V)) return rc;
+    V.default_label = default_label;
+    V.z0 = static_cast<long long>(h->z_begin);
+    // the index buffer keeps one plane above the slab (the fused step recomputes H' there); fill it when it exists globally
+    V.n_planes = static_cast<long long>(h->nzl + (h->z_end < h->nz ? 1 : 0));
+    int rc = h->idx_bytes == 1 ? scene_launch<uint8_t>(h, V, static_cast<uint8_t*>(h->mat), h->stream)
+                               : scene_launch<uint16_t>(h, V, static_cast<uint16_t*>(h->mat), h->stream);
+    if (rc) return rc;
+    h->launches += 1;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));   // the device copies of shapes/boxes die with `dev`
     return FDTD_B200_OK;
 }
 

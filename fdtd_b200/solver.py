@@ -213,6 +213,11 @@ class FdtdB200Backend:
         n = config.lattice_size()
         zb, ze = self.z_slab if self.z_slab else (0, n[2])
         lib = L.lib()
+        if hasattr(domain_description, "c_shapes"):
+            # scene.SceneDomain: rasterised on the device when the state is created — no host lattice, no per-cell callback
+            inst = FdtdB200SolverInstance(self, config, domain_description.palette, None)
+            inst.scene = domain_description
+            return inst
         if isinstance(domain_description, MaterialLattice):
             palette = domain_description.palette
             ids = domain_description.ids
@@ -251,6 +256,7 @@ class FdtdB200SolverInstance:
         self.config = config
         self.palette = list(palette)
         self.ids = ids
+        self.scene = None
         self.lattice = config.lattice_size()
 
     # -- SolverInstance -------------------------------------------------------------------------
@@ -262,7 +268,11 @@ class FdtdB200SolverInstance:
         idp = None if self.ids is None else self.ids.ctypes.data_as(C.POINTER(C.c_uint32))
         handle = C.c_void_p()
         L.check(lib.fdtd_b200_create(C.byref(cc), C.byref(pc), pal, len(self.palette), idp, C.byref(handle)))
-        return FdtdB200SolverState(self, handle)
+        state = FdtdB200SolverState(self, handle)
+        if self.scene is not None:
+            sc = self.scene
+            L.check(lib.fdtd_b200_set_materials_from_scene(handle, sc.c_transform(), sc.c_shapes(), len(sc.shapes), 0), handle)
+        return state
 
     def begin_update(self, state: "FdtdB200SolverState") -> "FdtdB200UpdatePass":
         return FdtdB200UpdatePass(self, state)

@@ -244,6 +244,32 @@ int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint6
  * work already enqueued on src's stream and before later work on dst's stream. */
 int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle src, int which_src);
 
+/* ---- scene → material lattice --------------------------------------------------------------- */
+
+/* One collider of the application's scene with the material label its entity carries.  Replaces the per-cell
+ * `DomainDescription::material(point)` callback (cpu/mod.rs:244-264) as the application implements it: lattice point →
+ * world (f64 matrix, cast to f32) → first collider containing the point, else the default material
+ * (cem-app/src/solver/runner.rs:606-631, 909-918).  Primitives are parry3d's Ball / Cuboid / Cylinder (axis = local Y). */
+enum { FDTD_B200_SHAPE_BALL = 0, FDTD_B200_SHAPE_CUBOID = 1, FDTD_B200_SHAPE_CYLINDER = 2 };
+typedef struct fdtd_b200_shape {
+    uint32_t kind;
+    uint32_t label;       /* palette index written to the cells whose point lies inside */
+    float params[3];      /* ball: radius | cuboid: half extents x,y,z | cylinder: half_height, radius */
+    float rot[9];         /* world → local rotation, row-major (inverse of the entity's rotation) */
+    float translation[3]; /* entity position in world units */
+    float reserved;
+} fdtd_b200_shape;
+
+/* Rasterise planes [z_begin, z_end) of an nx×ny×nz lattice on `device`: ids_out (host, (z_end-z_begin)*ny*nx u32, x
+ * fastest) receives, per cell, the label of the FIRST shape (array order) containing the cell's world point, else
+ * default_label.  solver_to_world: 4×4 row-major f64, last row 0 0 0 1 (`transform_from_solver_to_world`). */
+int fdtd_b200_rasterize_scene(int device, const uint64_t dims[3], uint64_t z_begin, uint64_t z_end, const double solver_to_world[16],
+                              const fdtd_b200_shape* shapes, uint32_t n_shapes, uint32_t default_label, uint32_t* ids_out);
+/* The same rasterisation written straight into the handle's device material index (its own slab and, on fused-step
+ * slabs, the plane above it) — no host lattice exists at any point.  Labels must be < the handle's table size. */
+int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_to_world[16], const fdtd_b200_shape* shapes,
+                                       uint32_t n_shapes, uint32_t default_label);
+
 /* ---- field access -------------------------------------------------------------------------- */
 
 /* `Field::field(...).iter()` over the half-open box [lo, hi) in GLOBAL coordinates clipped to the
