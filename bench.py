@@ -7,7 +7,8 @@ A "step" is one full leapfrog step (H half-step then E half-step, six components
 N = 1 : BASELINE configs[2] — the 512^3 heterogeneous lattice inside the lossy absorbing layer (SURVEY §8d
         config 3, the headline single-GPU roofline run).
 N > 1 : the same kind of lattice grown so every GPU keeps 512^3 cells (weak scaling), z-slab decomposed:
-        N=2 1024x512x512, N=4 1024x1024x512, N=8 1024^3; one-plane Hx,Hy / Ex,Ey halo per half-step over NCCL.
+        N=2 1024x512x512, N=4 1024x1024x512, N=8 1024^3; halo planes stored into the neighbours' ghost planes over NVLink peer
+        memory with device-side flags (--transport p2p, default) or exchanged with NCCL send/recv (--transport nccl).
 `--impl reference` times the CPU restatement of the reference's own CPU backend (oracle/, f64 AoS, all host
 threads) on a bounded z-slab sample of the same lattice; the Rust reference itself cannot be built here.
 Prints ONE JSON line on rank 0.
@@ -197,9 +198,29 @@ def run_b200(args) -> None:
     st = inst.create_state()
     st.register_probes(w.probes)
     stepper = None
+    transport = "none"
     if world > 1:
-        engine = CudaSlabEngine(st)
-        stepper = SlabStepper(engine, rank, world, overlap=not args.no_overlap)
+        from fdtd_b200.distributed import P2PSlabStepper
+
+        if args.transport == "p2p" and st.uses_fused:
+            # NVLink peer-memory halos (CUDA IPC + device-side flags, stepping inside the C library).  If the box refuses
+            # IPC mappings every rank falls back to NCCL together; the line says which transport ran.
+            try:
+                stepper = P2PSlabStepper(st, rank, world)
+                ok = 1.0
+            except Exception as exc:  # noqa: BLE001
+                print(f"[rank {rank}] p2p transport unavailable: {exc}", file=sys.stderr, flush=True)
+                ok = 0.0
+            t = torch.tensor([ok], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            if float(t.item()) < 1.0:
+                stepper = None
+            else:
+                transport = "p2p (CUDA IPC peer stores + device flags)"
+        if stepper is None:
+            engine = CudaSlabEngine(st)
+            stepper = SlabStepper(engine, rank, world, overlap=not args.no_overlap)
+            transport = "nccl send/recv"
 
     def advance(n):
         if stepper is None:
@@ -323,7 +344,7 @@ def run_b200(args) -> None:
                                   "Gaussian point source, 8 probes (BASELINE configs[2]; weak-scaled 512^3 cells per GPU for N>1)",
                       "lattice": [nx, ny, nz], "cells_per_gpu": cells_total // n_gpus, "decomposition": f"z-slabs x{n_gpus}",
                       "l2": "working set 25 B/cell x 134M cells per GPU >> 126 MB L2 (no flush needed)",
-                      "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap)},
+                      "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport},
            "roofline": roofline, "cpu_baseline": cpu_baseline,
            "e2e": {"value": e2e_value, "unit": "Gcells/s", "h2d_bytes_per_step": 32 * n_src, "d2h_bytes_per_step": 24 * n_pr,
                    "ms_per_step": 1e3 * e2e_s / K},
@@ -342,6 +363,7 @@ def main() -> None:
     ap.add_argument("--lattice", type=lambda s: [int(v) for v in s.split(",")], default=None)
     ap.add_argument("--exact", action="store_true", help="FDTD_B200_EXACT_ARITHMETIC kernels")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--transport", choices=("p2p", "nccl"), default="p2p", help="halo transport for N>1 (p2p needs the fused step)")
     ap.add_argument("--no-fused", action="store_true", help="two-kernel path (in-place, 24 B/cell of field memory) instead of the fused step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-planes", type=int, default=32, help="z-planes in the CPU legs' sample slab")

@@ -18,6 +18,7 @@ COLORMAP_CPU, COLORMAP_LINEAR, COLORMAP_APP_Z = 0, 1, 2
  HALO_SEND_EX_BOTTOM, HALO_SEND_EY_BOTTOM, HALO_SEND_EZ_BOTTOM, HALO_RECV_EX_HIGH, HALO_RECV_EY_HIGH, HALO_RECV_EZ_HIGH,
  HALO_SEND_MAT_BOTTOM, HALO_RECV_MAT_HIGH) = range(16)
 HALO_PENDING = 0x100
+P2P_BLOB_BYTES = 2048
 
 
 class Material(C.Structure):
@@ -98,6 +99,11 @@ SYMBOLS = {
     "fdtd_b200_fused_commit": (C.c_int, [_H]),
     "fdtd_b200_halo_plane": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p), _u64p]),
     "fdtd_b200_halo_copy": (C.c_int, [_H, C.c_int, _H, C.c_int]),
+    "fdtd_b200_p2p_export": (C.c_int, [_H, C.c_void_p]),
+    "fdtd_b200_p2p_connect": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "fdtd_b200_p2p_refresh": (C.c_int, [_H]),
+    "fdtd_b200_p2p_step": (C.c_int, [_H, C.c_uint64]),
+    "fdtd_b200_p2p_connected": (C.c_int, [_H]),
     "fdtd_b200_rasterize_scene": (C.c_int, [C.c_int, _u64p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32, _u32p]),
     "fdtd_b200_set_materials_from_scene": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32]),
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),

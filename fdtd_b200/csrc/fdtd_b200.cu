@@ -86,6 +86,21 @@ struct fdtd_b200_solver {
     cudaEvent_t timer_start = nullptr, timer_stop = nullptr;
     Tune tune;
     std::string err;
+
+    // NVLink peer-memory halo transport (fdtd_b200_p2p_*)
+    struct PeerLink {
+        bool present = false, same_process = false;
+        uint64_t nzl = 0;
+        float* field[2][6] = {};            // the neighbour's two buffer sets, each starting at its lower ghost plane
+        unsigned char* mat = nullptr;
+        unsigned long long* flags = nullptr;  // the neighbour's flag words
+        std::vector<void*> opened;          // cudaIpcOpenMemHandle results to close
+    } lower, upper;
+    unsigned long long* d_flags = nullptr;  // [0] pushes received from below, [1] from above, [2] flag-wait timeout marker
+    uint64_t halo_seq = 0;                  // pushes made to (and expected from) each neighbour so far
+    bool p2p = false, p2p_mat_sent = false;
+    cudaStream_t bstream = nullptr;         // high-priority stream of the boundary planes and the pushes
+    cudaEvent_t ev_main = nullptr, ev_bnd = nullptr, ev_push = nullptr;
 };
 
 namespace {
@@ -782,6 +797,13 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_probe_slot) cudaFree(h->d_probe_slot);
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
     if (h->d_stage) cudaFree(h->d_stage);
+    if (h->bstream) cudaStreamSynchronize(h->bstream);
+    for (auto* link : {&h->lower, &h->upper}) { for (void* p : link->opened) cudaIpcCloseMemHandle(p); link->opened.clear(); }
+    if (h->d_flags) cudaFree(h->d_flags);
+    if (h->ev_main) cudaEventDestroy(h->ev_main);
+    if (h->ev_bnd) cudaEventDestroy(h->ev_bnd);
+    if (h->ev_push) cudaEventDestroy(h->ev_push);
+    if (h->bstream) cudaStreamDestroy(h->bstream);
     prof_clear(h);
     if (h->timer_start) cudaEventDestroy(h->timer_start);
     if (h->timer_stop) cudaEventDestroy(h->timer_stop);
@@ -828,6 +850,12 @@ int fdtd_b200_sync(fdtd_b200_handle h) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
     if (int rc = set_device(h)) return rc;
     CU_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->bstream) CU_TRY(h, cudaStreamSynchronize(h->bstream));
+    if (h->d_flags) {
+        unsigned long long marker = 0;
+        CU_TRY(h, cudaMemcpy(&marker, h->d_flags + 2, sizeof marker, cudaMemcpyDeviceToHost));
+        if (marker) return fail(h, FDTD_B200_ECUDA, "timed out waiting for a neighbour's halo flag (push #" + std::to_string(marker) + "): ranks out of step?");
+    }
     return FDTD_B200_OK;
 }
 
@@ -1411,6 +1439,232 @@ int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_t
     if (rc) return rc;
     h->launches += 1;
     CU_TRY(h, cudaStreamSynchronize(h->stream));   // the device copies of shapes/boxes die with `dev`
+    return FDTD_B200_OK;
+}
+
+}  // extern "C"
+
+// ---- NVLink peer-memory halo transport ------------------------------------------------------------------------------------
+// SURVEY §8e "primary" transport: boundary planes are written into the neighbour's ghost planes through peer-mapped memory and
+// ordered by a release/acquire flag that lives in the receiver's HBM; nothing on the host synchronises per step.
+#include <unistd.h>
+
+namespace {
+
+struct P2PBlob {
+    uint32_t magic, version;
+    int32_t device;
+    uint32_t idx_bytes;
+    uint64_t pid;
+    uint64_t nx, ny, nz, z_begin, z_end;
+    cudaIpcMemHandle_t field[2][6], mat, flags;
+    uint64_t raw_field[2][6], raw_mat, raw_flags;
+};
+static_assert(sizeof(P2PBlob) <= FDTD_B200_P2P_BLOB_BYTES, "blob must fit the size the header promises");
+constexpr uint32_t P2P_MAGIC = 0xFD7DB200u;
+
+__global__ void k_wait_flag(const volatile unsigned long long* flag, unsigned long long want, unsigned long long* timeout_marker,
+                            long long max_cycles) {
+    const long long t0 = clock64();
+    while (*flag < want) {
+        if (clock64() - t0 > max_cycles) { atomicExch(timeout_marker, want); return; }   // never hang the GPU; sync() reports it
+        __nanosleep(200);
+    }
+    __threadfence_system();   // acquire: the planes pushed before the flag are visible to the kernels that follow
+}
+
+__global__ void k_signal_flag(volatile unsigned long long* peer_flag, unsigned long long value) {
+    __threadfence_system();   // release: this stream's earlier peer writes (the pushed planes) are ordered before the flag
+    *peer_flag = value;
+}
+
+float* set_base(fdtd_b200_handle h, int set, int c) { return set == h->cur_set ? h->alloc[c] : h->alt_alloc[c]; }
+
+int p2p_open(fdtd_b200_handle h, const P2PBlob& b, fdtd_b200_solver::PeerLink* link) {
+    link->present = true;
+    link->nzl = b.z_end - b.z_begin;
+    link->same_process = b.pid == static_cast<uint64_t>(getpid());
+    if (link->same_process) {
+        if (b.device != h->device) {
+            int can = 0;
+            CU_TRY(h, cudaDeviceCanAccessPeer(&can, h->device, b.device));
+            if (!can) return fail(h, FDTD_B200_ECUDA, "devices cannot access each other's memory (no NVLink/P2P path)");
+            const cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU_TRY(h, e);
+            (void)cudaGetLastError();
+        }
+        for (int s = 0; s < 2; ++s)
+            for (int c = 0; c < 6; ++c) link->field[s][c] = reinterpret_cast<float*>(b.raw_field[s][c]);
+        link->mat = reinterpret_cast<unsigned char*>(b.raw_mat);
+        link->flags = reinterpret_cast<unsigned long long*>(b.raw_flags);
+        return FDTD_B200_OK;
+    }
+    auto open = [&](const cudaIpcMemHandle_t& m, void** out) -> int {
+        CU_TRY(h, cudaIpcOpenMemHandle(out, m, cudaIpcMemLazyEnablePeerAccess));
+        link->opened.push_back(*out);
+        return FDTD_B200_OK;
+    };
+    void* p = nullptr;
+    for (int s = 0; s < 2; ++s)
+        for (int c = 0; c < 6; ++c) {
+            if (int rc = open(b.field[s][c], &p)) return rc;
+            link->field[s][c] = static_cast<float*>(p);
+        }
+    if (int rc = open(b.mat, &p)) return rc;
+    link->mat = static_cast<unsigned char*>(p);
+    if (int rc = open(b.flags, &p)) return rc;
+    link->flags = static_cast<unsigned long long*>(p);
+    return FDTD_B200_OK;
+}
+
+void p2p_close(fdtd_b200_solver::PeerLink* link) {
+    for (void* p : link->opened) cudaIpcCloseMemHandle(p);
+    link->opened.clear();
+    link->present = false;
+}
+
+// Store this slab's boundary planes of buffer set `set` into the neighbours' ghost planes of the same set, then raise their flags.
+int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st) {
+    const size_t plane_bytes = static_cast<size_t>(h->plane) * sizeof(float);
+    if (h->upper.present) {   // my top Ex,Ey → the upper slab's ghost plane below its plane 0
+        for (int c = 0; c < 2; ++c)
+            CU_TRY(h, cudaMemcpyAsync(h->upper.field[set][c], set_base(h, set, c) + h->plane * h->nzl, plane_bytes, cudaMemcpyDeviceToDevice, st));
+    }
+    if (h->lower.present) {   // my whole first plane (E and Hx,Hy) → the lower slab's ghost plane above its last plane
+        for (int c = 0; c < 5; ++c)
+            CU_TRY(h, cudaMemcpyAsync(h->lower.field[set][c] + h->plane * (h->lower.nzl + 1), set_base(h, set, c) + h->plane, plane_bytes,
+                                      cudaMemcpyDeviceToDevice, st));
+        if (!h->p2p_mat_sent)
+            CU_TRY(h, cudaMemcpyAsync(h->lower.mat + h->plane * h->lower.nzl * h->idx_bytes, h->mat, h->plane * h->idx_bytes, cudaMemcpyDeviceToDevice, st));
+    }
+    h->p2p_mat_sent = true;
+    h->halo_seq += 1;
+    if (h->upper.present) k_signal_flag<<<1, 1, 0, st>>>(h->upper.flags + 0, h->halo_seq);   // "received from below"
+    if (h->lower.present) k_signal_flag<<<1, 1, 0, st>>>(h->lower.flags + 1, h->halo_seq);   // "received from above"
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+int p2p_wait(fdtd_b200_handle h, cudaStream_t st) {
+    if (h->halo_seq == 0) return FDTD_B200_OK;
+    const long long max_cycles = 10LL * 1900000000LL;   // ≈ 10 s at 1.9 GHz
+    if (h->lower.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 0, h->halo_seq, h->d_flags + 2, max_cycles);
+    if (h->upper.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 1, h->halo_seq, h->d_flags + 2, max_cycles);
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fdtd_b200_p2p_connected(fdtd_b200_handle h) { return h && h->p2p ? 1 : 0; }
+
+int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob) {
+    if (!h || !blob) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport needs a fused-step handle (FDTD_B200_FUSED_STEP on an eligible lattice)");
+    if (int rc = set_device(h)) return rc;
+    if (!h->d_flags) {
+        CU_TRY(h, cudaMalloc(&h->d_flags, 64));
+        CU_TRY(h, cudaMemset(h->d_flags, 0, 64));
+    }
+    P2PBlob b;
+    std::memset(&b, 0, sizeof b);
+    b.magic = P2P_MAGIC; b.version = 1; b.device = h->device; b.idx_bytes = static_cast<uint32_t>(h->idx_bytes);
+    b.pid = static_cast<uint64_t>(getpid());
+    b.nx = h->nx; b.ny = h->ny; b.nz = h->nz; b.z_begin = h->z_begin; b.z_end = h->z_end;
+    for (int s = 0; s < 2; ++s)
+        for (int c = 0; c < 6; ++c) {
+            float* base = set_base(h, s, c);
+            b.raw_field[s][c] = reinterpret_cast<uint64_t>(base);
+            CU_TRY(h, cudaIpcGetMemHandle(&b.field[s][c], base));
+        }
+    b.raw_mat = reinterpret_cast<uint64_t>(h->mat);
+    b.raw_flags = reinterpret_cast<uint64_t>(h->d_flags);
+    CU_TRY(h, cudaIpcGetMemHandle(&b.mat, h->mat));
+    CU_TRY(h, cudaIpcGetMemHandle(&b.flags, h->d_flags));
+    std::memset(blob, 0, FDTD_B200_P2P_BLOB_BYTES);
+    std::memcpy(blob, &b, sizeof b);
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_p2p_connect(fdtd_b200_handle h, const void* lower_blob, const void* upper_blob) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (!h->fused || !h->d_flags) return fail(h, FDTD_B200_ESTATE, "call fdtd_b200_p2p_export on this (fused-step) handle first");
+    if ((h->z_begin > 0) != (lower_blob != nullptr) || (h->z_end < h->nz) != (upper_blob != nullptr))
+        return fail(h, FDTD_B200_EINVAL, "a neighbour blob is required exactly where the slab has a neighbour");
+    if (int rc = set_device(h)) return rc;
+    p2p_close(&h->lower);
+    p2p_close(&h->upper);
+    h->p2p = false;
+    for (int side = 0; side < 2; ++side) {
+        const void* src = side == 0 ? lower_blob : upper_blob;
+        if (!src) continue;
+        P2PBlob b;
+        std::memcpy(&b, src, sizeof b);
+        if (b.magic != P2P_MAGIC || b.version != 1) return fail(h, FDTD_B200_EINVAL, "not a fdtd_b200 p2p blob");
+        if (b.nx != h->nx || b.ny != h->ny || b.nz != h->nz || b.idx_bytes != static_cast<uint32_t>(h->idx_bytes))
+            return fail(h, FDTD_B200_EINVAL, "neighbour blob describes a different lattice");
+        if (side == 0 ? b.z_end != h->z_begin : b.z_begin != h->z_end) return fail(h, FDTD_B200_EINVAL, "neighbour slab is not adjacent");
+        if (int rc = p2p_open(h, b, side == 0 ? &h->lower : &h->upper)) return rc;
+    }
+    if (!h->bstream) {
+        int lo = 0, hi = 0;
+        CU_TRY(h, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU_TRY(h, cudaStreamCreateWithPriority(&h->bstream, cudaStreamNonBlocking, hi));
+        CU_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
+        CU_TRY(h, cudaEventCreateWithFlags(&h->ev_bnd, cudaEventDisableTiming));
+        CU_TRY(h, cudaEventCreateWithFlags(&h->ev_push, cudaEventDisableTiming));
+    }
+    h->p2p = true;
+    h->p2p_mat_sent = false;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_p2p_refresh(fdtd_b200_handle h) {
+    if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
+    if (int rc = set_device(h)) return rc;
+    // asynchronous and flag-ordered: the next p2p_step's boundary launch waits on the device for the neighbours' copies
+    return p2p_push(h, h->cur_set, h->stream);
+}
+
+int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
+    if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
+    if (int rc = set_device(h)) return rc;
+    const int n = static_cast<int>(h->nzl);
+    const bool split = n >= 3;                      // otherwise the whole slab is "boundary"
+    const int lo = (split && h->lower.present) ? 1 : 0;
+    const int hi = (split && h->upper.present) ? n - 1 : n;
+    cudaStream_t S = h->stream, B = h->bstream;
+    // whatever was enqueued on the main stream before (uploads, earlier steps, a refresh) precedes the first boundary launch
+    CU_TRY(h, cudaEventRecord(h->ev_main, S));
+    for (uint64_t s = 0; s < n_steps; ++s) {
+        // boundary stream: previous interior done → neighbours' pushes of the previous step arrived → boundary planes → push
+        CU_TRY(h, cudaStreamWaitEvent(B, h->ev_main, 0));
+        if (int rc = p2p_wait(h, B)) return rc;
+        h->stream = B;
+        int rc = FDTD_B200_OK;
+        if (!split) rc = launch_fused(h, 0, n);
+        else {
+            if (hi < n) rc = launch_fused(h, hi, n);
+            if (!rc && lo > 0) rc = launch_fused(h, 0, lo);
+        }
+        h->stream = S;
+        if (rc) return rc;
+        CU_TRY(h, cudaEventRecord(h->ev_bnd, B));
+        if (int rc2 = p2p_push(h, h->cur_set ^ 1, B)) return rc2;   // the planes just written live in the pending set
+        CU_TRY(h, cudaEventRecord(h->ev_push, B));
+        // main stream: interior planes, concurrently with the boundary work above (they read the same current set and write
+        // disjoint planes of the pending set); the previous step's boundary planes are ordered by ev_bnd from the last turn
+        if (split && lo < hi) {
+            if (int rc3 = launch_fused(h, lo, hi)) return rc3;
+        }
+        CU_TRY(h, cudaStreamWaitEvent(S, h->ev_bnd, 0));            // the next interior launch reads this step's boundary planes
+        CU_TRY(h, cudaEventRecord(h->ev_main, S));
+        commit_fused(h);
+        end_step(h);
+    }
+    CU_TRY(h, cudaStreamWaitEvent(S, h->ev_push, 0));               // sync()/timer on the main stream cover the last pushes too
     return FDTD_B200_OK;
 }
 

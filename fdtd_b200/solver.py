@@ -346,6 +346,25 @@ class FdtdB200SolverState:
     def update_e(self, z_lo: int, z_hi: int) -> None:
         L.check(self._lib.fdtd_b200_update_e(self._h, z_lo, z_hi), self._h)
 
+    # NVLink peer-memory halo transport (include/fdtd_b200.h "fdtd_b200_p2p_*")
+    def p2p_export(self) -> bytes:
+        buf = C.create_string_buffer(L.P2P_BLOB_BYTES)
+        L.check(self._lib.fdtd_b200_p2p_export(self._h, buf), self._h)
+        return buf.raw
+
+    def p2p_connect(self, lower_blob: Optional[bytes], upper_blob: Optional[bytes]) -> None:
+        L.check(self._lib.fdtd_b200_p2p_connect(self._h, lower_blob, upper_blob), self._h)
+
+    def p2p_refresh(self) -> None:
+        L.check(self._lib.fdtd_b200_p2p_refresh(self._h), self._h)
+
+    def p2p_step(self, n_steps: int = 1) -> None:
+        L.check(self._lib.fdtd_b200_p2p_step(self._h, int(n_steps)), self._h)
+
+    @property
+    def p2p_connected(self) -> bool:
+        return bool(self._lib.fdtd_b200_p2p_connected(self._h))
+
     def fused_update(self, z_lo: int, z_hi: int) -> None:
         L.check(self._lib.fdtd_b200_fused_update(self._h, z_lo, z_hi), self._h)
 

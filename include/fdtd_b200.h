@@ -244,6 +244,26 @@ int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint6
  * work already enqueued on src's stream and before later work on dst's stream. */
 int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle src, int which_src);
 
+/* ---- NVLink peer-memory halo transport (one process per GPU, no NCCL, no host synchronisation per step) ----
+ * Fused-step slab handles only.  Every rank exports a blob describing its device allocations (CUDA IPC memory handles; raw
+ * pointers when both handles live in one process), the caller moves the blobs between z-neighbours by any out-of-band
+ * channel (torch.distributed all_gather in fdtd_b200/distributed.py), and connect maps the neighbours' ghost planes.
+ * fdtd_b200_p2p_step then runs n leapfrog steps: the slab's boundary planes are updated first on a high-priority stream,
+ * stored straight into the neighbours' ghost planes over NVLink (SURVEY §8e "primary" transport), followed by a release
+ * flag in the neighbour's memory; the neighbour's next boundary launch acquires that flag on the device; the interior
+ * planes run concurrently on the main stream.  All ranks must make the same sequence of p2p_refresh / p2p_step calls. */
+#define FDTD_B200_P2P_BLOB_BYTES 2048
+int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob /* FDTD_B200_P2P_BLOB_BYTES */);
+/* lower_blob / upper_blob: blobs of the ranks owning the slab below / above (NULL where the lattice ends). */
+int fdtd_b200_p2p_connect(fdtd_b200_handle h, const void* lower_blob, const void* upper_blob);
+/* Push the CURRENT boundary planes (and, once, the material index of the first plane) into the neighbours' ghost planes
+ * — after connect, reset and after fields were written from outside.  Asynchronous: ordered against the neighbours' steps by
+ * the same device-side flags, so no host barrier is needed as long as every rank calls it at the same point. */
+int fdtd_b200_p2p_refresh(fdtd_b200_handle h);
+int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps);
+/* 1 when connect succeeded and p2p_step may be called. */
+int fdtd_b200_p2p_connected(fdtd_b200_handle h);
+
 /* ---- scene → material lattice --------------------------------------------------------------- */
 
 /* One collider of the application's scene with the material label its entity carries.  Replaces the per-cell

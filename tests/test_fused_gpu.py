@@ -154,3 +154,76 @@ def test_fused_two_slabs_equal_one_domain(b200, tune, size, cut, ranges):
         got = np.concatenate([lo.read_field(comp), hi.read_field(comp)], axis=0)
         assert np.array_equal(got, whole.read_field(comp))
     assert np.array_equal(lo.read_probes(0, steps) + hi.read_probes(0, steps), s_whole)
+
+
+@pytest.mark.parametrize("size,cuts", [((128, 9, 12), (4, 9)), ((256, 5, 9), (4,)), ((128, 8, 7), (1, 3)), ((128, 6, 6), (2, 4))])
+def test_p2p_slab_steps_equal_one_domain(b200, tune, size, cuts):
+    """The peer-memory transport (fdtd_b200_p2p_*) with all slab handles in ONE process on one GPU (blobs carry raw pointers
+    then): boundary planes first on the high-priority stream, stores into the neighbours' ghost planes, device-side flags.
+    Two and three slabs (a middle slab has both neighbours; 1- and 2-plane slabs have no interior launch), sources and probes
+    at the cuts, a reset + refresh in the middle: bit-identical to the whole-domain fused run."""
+    tune(None)
+    w = _random_workload(b200, size, seed=43)
+    nz = size[2]
+    c0 = cuts[0]
+    w.sources = [((size[0] // 2, size[1] // 2, c0), w.sources[0][1]), ((5, 1, c0 - 1), b200.GaussianPulse(0.2, 0.5).with_amplitudes((1, 2, 3), (-1, 0.5, 2)))]
+    probes = [(size[0] // 2, size[1] // 2, c0 - 1), (3, 2, c0), (size[0] - 1, size[1] - 1, nz - 1)]
+    init = random_fields(w, seed=15)
+    steps = 6
+    tab = w.source_table(steps)
+    bounds = list(zip((0,) + tuple(cuts), tuple(cuts) + (nz,)))
+
+    def load(st, a, b):
+        st.write_field(b200.FieldComponent.E, init[0][a:b], (0, 0, a), (size[0], size[1], b))
+        st.write_field(b200.FieldComponent.H, init[1][a:b], (0, 0, a), (size[0], size[1], b))
+        st.register_probes(probes)
+        st.set_source_table(w.source_points(), tab)
+
+    slabs = []
+    for a, b in bounds:
+        st = b200.FdtdB200Backend(exact_arithmetic=True, fused_step=True, z_slab=(a, b)).create_instance(w.solver_config(), w.domain()).create_state()
+        assert st.uses_fused and not st.p2p_connected
+        slabs.append(st)
+    blobs = [st.p2p_export() for st in slabs]
+    for k, st in enumerate(slabs):
+        st.p2p_connect(blobs[k - 1] if k > 0 else None, blobs[k + 1] if k + 1 < len(slabs) else None)
+        assert st.p2p_connected
+    for rnd in range(2):   # second round: reset, reload, refresh — the flag sequence keeps counting
+        whole, s_whole = run(b200, w, steps, exact=True, fused=True, init=init, probes=probes)
+        for st, (a, b) in zip(slabs, bounds):
+            if rnd:
+                st.reset()
+            load(st, a, b)
+        for st in slabs:
+            st.p2p_refresh()
+        for _ in range(steps):          # one step per handle and turn: a single host thread must keep the slabs in lockstep
+            for st in slabs:
+                st.p2p_step(1)
+        for st in slabs:
+            st.sync()
+            assert st.tick() == steps
+        for comp in (b200.FieldComponent.E, b200.FieldComponent.H):
+            got = np.concatenate([st.read_field(comp) for st in slabs], axis=0)
+            assert np.array_equal(got, whole.read_field(comp))
+        assert np.array_equal(sum(st.read_probes(0, steps) for st in slabs), s_whole)
+
+
+def test_p2p_argument_errors(b200, tune):
+    from fdtd_b200 import _lib as L
+
+    tune(None)
+    w = _random_workload(b200, (128, 8, 8), seed=3)
+    plain = b200.FdtdB200Backend(z_slab=(0, 4)).create_instance(w.solver_config(), w.domain()).create_state()
+    with pytest.raises(L.Fdtd_b200Error):
+        plain.p2p_export()                                   # not a fused-step handle
+    a = b200.FdtdB200Backend(fused_step=True, z_slab=(0, 4)).create_instance(w.solver_config(), w.domain()).create_state()
+    b = b200.FdtdB200Backend(fused_step=True, z_slab=(5, 8)).create_instance(w.solver_config(), w.domain()).create_state()
+    with pytest.raises(L.Fdtd_b200Error):
+        a.p2p_step(1)                                        # not connected
+    ba, bb = a.p2p_export(), b.p2p_export()
+    with pytest.raises(L.Fdtd_b200Error):
+        a.p2p_connect(None, bb)                              # slabs are not adjacent
+    with pytest.raises(L.Fdtd_b200Error):
+        a.p2p_connect(None, None)                            # a neighbour blob is required above
+    with pytest.raises(L.Fdtd_b200Error):
+        a.p2p_connect(None, b"\0" * L.P2P_BLOB_BYTES)

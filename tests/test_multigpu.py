@@ -10,12 +10,12 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("overlap,fused", [("1", "0"), ("0", "0"), ("1", "1"), ("0", "1")])
-def test_two_ranks_bit_identical_to_one(b200, overlap, fused):
+@pytest.mark.parametrize("overlap,fused,transport", [("1", "0", "nccl"), ("0", "0", "nccl"), ("1", "1", "nccl"), ("0", "1", "nccl"), ("1", "1", "p2p")])
+def test_two_ranks_bit_identical_to_one(b200, overlap, fused, transport):
     n = b200.lib().fdtd_b200_device_count()
     if n < 2:
         pytest.skip("needs two GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29571", os.path.join(ROOT, "tools", "slab_parity.py"), "128,48,40" if fused == "1" else "64,48,40", "25", overlap, fused]
+           "--master-port", "29571", os.path.join(ROOT, "tools", "slab_parity.py"), "128,48,40" if fused == "1" else "64,48,40", "25", overlap, fused, transport]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]

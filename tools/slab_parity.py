@@ -22,6 +22,7 @@ def main():
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 25
     overlap = (sys.argv[3] != "0") if len(sys.argv) > 3 else True
     fused = (sys.argv[4] != "0") if len(sys.argv) > 4 else False
+    transport = sys.argv[5] if len(sys.argv) > 5 else "nccl"     # nccl | p2p (NVLink peer memory, fused handles only)
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     zb, ze = partition_z(lattice[2], world)[rank]
@@ -36,7 +37,13 @@ def main():
     st = be.create_instance(w.solver_config(), w.domain()).create_state()
     st.register_probes(w.probes)
     st.set_source_table(w.source_points(), tab)
-    stepper = SlabStepper(CudaSlabEngine(st), rank, world, overlap=overlap)
+    if transport == "p2p":
+        from fdtd_b200.distributed import P2PSlabStepper
+
+        stepper = P2PSlabStepper(st, rank, world)
+        stepper.exchanges = steps
+    else:
+        stepper = SlabStepper(CudaSlabEngine(st), rank, world, overlap=overlap)
     stepper.step(steps)
     st.sync()
     torch.cuda.synchronize()
@@ -61,7 +68,7 @@ def main():
         eg, hg = torch.cat(es).cpu().numpy(), torch.cat(hs).cpu().numpy()
         ok = np.array_equal(eg, ef) and np.array_equal(hg, hf) and np.array_equal(pr.cpu().numpy(), full.read_probes(0, steps))
         ok = ok and bool(np.any(ef)) and st.tick() == steps
-        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} fused={st.uses_fused} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
+        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} fused={st.uses_fused} transport={transport} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
