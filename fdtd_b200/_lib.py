@@ -78,6 +78,7 @@ SYMBOLS = {
     "fdtd_b200_sync": (C.c_int, [_H]),
     "fdtd_b200_tick": (C.c_uint64, [_H]),
     "fdtd_b200_time": (C.c_double, [_H]),
+    "fdtd_b200_set_time": (C.c_int, [_H, C.c_uint64, C.c_double]),
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
     "fdtd_b200_uses_bulk": (C.c_int, [_H]),

@@ -859,6 +859,16 @@ int fdtd_b200_sync(fdtd_b200_handle h) {
     return FDTD_B200_OK;
 }
 
+int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (!std::isfinite(time)) return fail(h, FDTD_B200_EINVAL, "time must be finite");
+    h->tick = tick;
+    h->time = time;
+    h->n_src = 0; h->src_rows = 0; h->src_row = 0;
+    h->probe_first_tick = tick;
+    return FDTD_B200_OK;
+}
+
 uint64_t fdtd_b200_tick(fdtd_b200_handle h) { return h ? h->tick : 0; }
 double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
 int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }

@@ -320,6 +320,9 @@ class FdtdB200SolverState:
     def tick(self) -> int:
         return int(self._lib.fdtd_b200_tick(self._h))
 
+    def set_time(self, tick: int, time: float) -> None:
+        L.check(self._lib.fdtd_b200_set_time(self._h, int(tick), float(time)), self._h)
+
     # batched API
     def cell_index(self, point: Point) -> int:
         n = self.lattice
@@ -565,6 +568,10 @@ class ImageTarget:
     def size(self) -> tuple:
         return self.image.shape[1], self.image.shape[0]
 
+    def with_image_buffer(self, f) -> None:
+        """`FdtdImageTarget::with_image_buffer` (project.rs:136-151): hand the renderer this target's buffer."""
+        f(self.image)
+
 
 _APP_Z_SNIPPET_MARK = "var x = value.z"
 
@@ -596,10 +603,12 @@ class B200ProjectionPass:
         p = projection.parameters
         pm = np.ascontiguousarray(np.asarray(p.projection, dtype=np.float32).T)  # → column-major
         cm = np.ascontiguousarray(np.asarray(p.color_map, dtype=np.float32).T)
-        img = projection.target.image
-        try:
+        def render(img: np.ndarray) -> None:
             L.check(st._lib.fdtd_b200_project(st._h, p.field, pm.ctypes.data_as(C.POINTER(C.c_float)), cm.ctypes.data_as(C.POINTER(C.c_float)),
                                               projection.mode, img.shape[1], img.shape[0], img.ctypes.data_as(C.c_void_p), 0), st._h)
+
+        try:
+            projection.target.with_image_buffer(render)   # ImageTarget, io.GifEncoder, io.PngSequence …
         except L.Fdtd_b200Error as e:  # collected like cpu/project.rs:185-189
             self.errors.append(e)
 

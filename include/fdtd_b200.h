@@ -164,6 +164,9 @@ int fdtd_b200_sync(fdtd_b200_handle h);
 /* `Time` (lib.rs:92-95).  time is accumulated `time += dt` in f64 (cpu/mod.rs:513). */
 uint64_t fdtd_b200_tick(fdtd_b200_handle h);
 double fdtd_b200_time(fdtd_b200_handle h);
+/* Restore tick/time of a checkpointed state (fields come back through fdtd_b200_write_field).  Drops pending forcing
+ * rows and restarts the probe ring at `tick`. */
+int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time);
 
 /* Introspection used by tests and the bench. */
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
