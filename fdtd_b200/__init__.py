@@ -8,8 +8,8 @@ from ._lib import (COLORMAP_APP_Z, COLORMAP_CPU, COLORMAP_LINEAR, EXACT_ARITHMET
                    Fdtd_b200Error, lib)
 from .solver import (B200FieldView, B200Projection, B200ProjectionPass, ContinousWave, DomainDescription,
                      FdtdB200Backend, FdtdB200SolverInstance, FdtdB200SolverState, FdtdB200UpdatePass,
-                     FdtdSolverConfig, FieldComponent, GaussianPulse, ImageTarget, Material, MaterialLattice,
-                     PhysicalConstants, ProjectionParameters, Resolution, SourceValues, WithAmplitudes,
+                     FdtdSolverConfig, FieldComponent, GaussianPulse, GradedPml, ImageTarget, Material, MaterialLattice,
+                     PhysicalConstants, PmlCoefficients, PmlProfiles, ProjectionParameters, Resolution, SourceValues, WithAmplitudes,
                      normalize_point_bounds)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -44,6 +44,10 @@ class Config(C.Structure):
                 ("probe_ring_steps", C.c_uint32), ("reserved", C.c_uint32)]
 
 
+class GradedPml(C.Structure):
+    _fields_ = [("m", C.c_double), ("m_a", C.c_double), ("sigma_max", C.c_double), ("kappa_max", C.c_double), ("a_max", C.c_double)]
+
+
 class Source(C.Structure):
     _fields_ = [("cell", C.c_uint64), ("j", C.c_float * 3), ("m", C.c_float * 3)]
 
@@ -60,6 +64,7 @@ _H = C.c_void_p
 _u64p = C.POINTER(C.c_uint64)
 _u32p = C.POINTER(C.c_uint32)
 _fp = C.POINTER(C.c_float)
+_dp = C.POINTER(C.c_double)
 SYMBOLS = {
     "fdtd_b200_abi_version": (C.c_int, []),
     "fdtd_b200_device_count": (C.c_int, []),
@@ -79,6 +84,13 @@ SYMBOLS = {
     "fdtd_b200_tick": (C.c_uint64, [_H]),
     "fdtd_b200_time": (C.c_double, [_H]),
     "fdtd_b200_set_time": (C.c_int, [_H, C.c_uint64, C.c_double]),
+    "fdtd_b200_pml_coefficients": (C.c_int, [C.c_double, C.POINTER(PhysicalConstants), C.c_double, C.c_double, C.c_double, _dp, _dp, _dp]),
+    "fdtd_b200_pml_coefficients_graded": (C.c_int, [C.c_double, C.POINTER(PhysicalConstants), C.POINTER(GradedPml), C.c_double, _dp, _dp, _dp]),
+    "fdtd_b200_set_pml": (C.c_int, [_H, C.c_int, _dp, _dp, _dp, _dp]),
+    "fdtd_b200_has_pml": (C.c_int, [_H]),
+    "fdtd_b200_pml_state_floats": (C.c_uint64, [_H]),
+    "fdtd_b200_read_pml_state": (C.c_int, [_H, _fp]),
+    "fdtd_b200_write_pml_state": (C.c_int, [_H, _fp]),
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
     "fdtd_b200_uses_bulk": (C.c_int, [_H]),

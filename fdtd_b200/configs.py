@@ -26,12 +26,16 @@ class Workload:
     probes: list = field(default_factory=list)   # [point]
     steps: int = 0
     scene: Optional[object] = None      # scene.SceneDomain: the lattice is rasterised on the device (then `ids` is None)
+    pml: Optional[object] = None        # solver.PmlProfiles: CPML slabs; None = no PML, as the reference executes
 
     def solver_config(self) -> FdtdSolverConfig:
         return FdtdSolverConfig.from_lattice(self.lattice, self.resolution, self.constants)
 
     def domain(self):
-        return self.scene if self.scene is not None else MaterialLattice(self.palette, self.ids)
+        if self.scene is not None:
+            self.scene.pml_profiles = self.pml
+            return self.scene
+        return MaterialLattice(self.palette, self.ids, pml=self.pml)
 
     @property
     def n_cells(self) -> int:

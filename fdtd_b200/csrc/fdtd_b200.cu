@@ -17,6 +17,7 @@
 #include "kernels_bulk.cuh"
 #include "kernels_fused.cuh"
 #include "kernels_scene.cuh"
+#include "kernels_pml.cuh"
 
 using namespace fdtd_b200;
 
@@ -86,6 +87,18 @@ struct fdtd_b200_solver {
     cudaEvent_t timer_start = nullptr, timer_stop = nullptr;
     Tune tune;
     std::string err;
+
+    // CPML (fdtd_b200_set_pml): per axis the owned PML coordinates, their (b, c) and the ψ arrays of the slabs
+    struct PmlAxis {
+        int n = 0;                     // PML coordinates along the axis owned by this handle
+        std::vector<int> pos;          // local coordinates, ascending (host copy of d_pos)
+        std::vector<char> h_active;    // c of the H half-step is non-zero at pos[k]
+        int* d_pos = nullptr;
+        float2* d_bc[2] = {nullptr, nullptr};  // [0] H half-step, [1] E half-step
+        float* psi[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [half-step][G_ab, G_ac]
+        size_t floats = 0;             // length of each ψ array
+    } pml[3];
+    bool has_pml = false;
 
     // NVLink peer-memory halo transport (fdtd_b200_p2p_*)
     struct PeerLink {
@@ -454,6 +467,137 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     return FDTD_B200_OK;
 }
 
+// ---- CPML passes ---------------------------------------------------------------------------------
+
+void pml_free_axis(fdtd_b200_handle h, int a) {
+    auto& A = h->pml[a];
+    if (A.d_pos) cudaFree(A.d_pos);
+    for (int k = 0; k < 2; ++k) if (A.d_bc[k]) cudaFree(A.d_bc[k]);
+    for (int fld = 0; fld < 2; ++fld) for (int g = 0; g < 2; ++g) if (A.psi[fld][g]) cudaFree(A.psi[fld][g]);
+    A = fdtd_b200_solver::PmlAxis{};
+    h->has_pml = h->pml[0].n || h->pml[1].n || h->pml[2].n;
+}
+
+template <int FIELD, int AXIS, typename IdxT>
+int launch_pml_axis(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
+    const auto& A = h->pml[AXIS];
+    if (A.n == 0) return FDTD_B200_OK;
+    PmlAxisView P{};
+    P.n = A.n; P.pos = A.d_pos; P.bc = A.d_bc[FIELD]; P.g0 = A.psi[FIELD][0]; P.g1 = A.psi[FIELD][1]; P.k0 = 0;
+    int r0, r1, r2;
+    if (AXIS == 0) { r0 = A.n; r1 = L.ny; r2 = z_hi - z_lo; }
+    else if (AXIS == 1) { r0 = L.nx; r1 = A.n; r2 = z_hi - z_lo; }
+    else {
+        const auto lo = std::lower_bound(A.pos.begin(), A.pos.end(), z_lo);
+        const auto hi = std::lower_bound(A.pos.begin(), A.pos.end(), z_hi);
+        P.k0 = static_cast<int>(lo - A.pos.begin());
+        r0 = L.nx; r1 = L.ny; r2 = static_cast<int>(hi - lo);
+    }
+    if (r2 <= 0) return FDTD_B200_OK;
+    const float* s0 = FIELD == 0 ? L.ex : L.hx; const float* s1 = FIELD == 0 ? L.ey : L.hy; const float* s2 = FIELD == 0 ? L.ez : L.hz;
+    float* d0 = FIELD == 0 ? L.hx : L.ex; float* d1 = FIELD == 0 ? L.hy : L.ey; float* d2 = FIELD == 0 ? L.hz : L.ez;
+    const dim3 block(32, 8, 1);
+    for (int zz = 0; zz < r2; zz += 65535) {  // gridDim.z limit
+        const int nzz = std::min(r2 - zz, 65535);
+        const dim3 grid((r0 + 31) / 32, (r1 + 7) / 8, nzz);
+        PmlAxisView Q = P;
+        int zl = z_lo;
+        if (AXIS == 2) Q.k0 = P.k0 + zz; else zl = z_lo + zz;
+        k_pml_axis<FIELD, AXIS, IdxT><<<grid, block, 0, h->stream>>>(L, Q, s0, s1, s2, d0, d1, d2, zl, z_hi);
+        h->launches += 1;
+    }
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+// ψ recursion + correction of planes [z_lo, z_hi) after the half-step `FIELD` (0 = H, 1 = E) ran on them.  `L` names the
+// buffers: the E (H) pointers are differentiated, the H (E) pointers corrected.
+template <int FIELD>
+int launch_pml_on(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
+    int rc;
+    if (h->idx_bytes == 1) {
+        if ((rc = launch_pml_axis<FIELD, 0, uint8_t>(h, L, z_lo, z_hi))) return rc;
+        if ((rc = launch_pml_axis<FIELD, 1, uint8_t>(h, L, z_lo, z_hi))) return rc;
+        if ((rc = launch_pml_axis<FIELD, 2, uint8_t>(h, L, z_lo, z_hi))) return rc;
+    } else {
+        if ((rc = launch_pml_axis<FIELD, 0, uint16_t>(h, L, z_lo, z_hi))) return rc;
+        if ((rc = launch_pml_axis<FIELD, 1, uint16_t>(h, L, z_lo, z_hi))) return rc;
+        if ((rc = launch_pml_axis<FIELD, 2, uint16_t>(h, L, z_lo, z_hi))) return rc;
+    }
+    return FDTD_B200_OK;
+}
+
+int sample_probes(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
+    if (!h->n_probes_local) return FDTD_B200_OK;
+    const ProbeView P = probe_view(h);
+    k_sample_probes<<<(P.n + 127) / 128, 128, 0, h->stream>>>(L, P, z_lo, z_hi);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+// two-kernel path: in place
+template <int FIELD>
+int launch_pml(fdtd_b200_handle h, int z_lo, int z_hi) {
+    if (!h->has_pml) return FDTD_B200_OK;
+    const LatticeView L = lattice_view(h);
+    if (int rc = launch_pml_on<FIELD>(h, L, z_lo, z_hi)) return rc;
+    // the E kernel sampled the probes before the correction: sample again
+    return FIELD == 1 ? sample_probes(h, L, z_lo, z_hi) : FDTD_B200_OK;
+}
+
+int arithmetic_mode(fdtd_b200_handle h);
+
+template <int EXACT, typename IdxT>
+int launch_e_box(fdtd_b200_handle h, const LatticeView& L, float* const out[3], const CellBox& B) {
+    const ForcingView F = forcing_view(h);
+    const dim3 block(32, 8, 1);
+    const dim3 grid((B.x1 - B.x0 + 31) / 32, (B.y1 - B.y0 + 7) / 8, std::min(B.z1 - B.z0, 65535));
+    k_update_e_box<EXACT, IdxT><<<grid, block, 0, h->stream>>>(L, F, out[0], out[1], out[2], B);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+// Fused step with a PML (whole-lattice handles): the fused kernel wrote H'_0, E'_0 of the pending set without ψ.  Then
+//   1. H pass of the PML: ψ_H from the old E (current set), H'(pending) corrected in the slabs;
+//   2. E' recomputed out of place (old E of the current set, corrected H') wherever one of its H' operands changed:
+//      coordinates p with p or p+1 in the H slabs of an axis;
+//   3. E pass of the PML on the pending set; probes sampled from the pending set.
+int fused_pml_passes(fdtd_b200_handle h) {
+    const int nzl = static_cast<int>(h->nzl);
+    LatticeView L = lattice_view(h);            // E = current set (old), H = pending set
+    L.hx = h->g[3]; L.hy = h->g[4]; L.hz = h->g[5];
+    if (int rc = launch_pml_on<0>(h, L, 0, nzl)) return rc;
+    float* const out[3] = {h->g[0], h->g[1], h->g[2]};
+    const int mode = arithmetic_mode(h);
+    const int ext[3] = {L.nx, L.ny, L.nz};
+    for (int a = 0; a < 3; ++a) {
+        const auto& A = h->pml[a];
+        std::vector<char> touched(static_cast<size_t>(ext[a]) + 1, 0);
+        for (int k = 0; k < A.n; ++k) {
+            if (!A.h_active[k]) continue;
+            touched[A.pos[k]] = 1;
+            if (A.pos[k] > 0) touched[A.pos[k] - 1] = 1;
+        }
+        for (int lo = 0; lo < ext[a];) {
+            if (!touched[lo]) { ++lo; continue; }
+            int hi = lo;
+            while (hi < ext[a] && touched[hi]) ++hi;
+            CellBox B{0, L.nx, 0, L.ny, 0, L.nz};
+            if (a == 0) { B.x0 = lo; B.x1 = hi; } else if (a == 1) { B.y0 = lo; B.y1 = hi; } else { B.z0 = lo; B.z1 = hi; }
+            int rc;
+            if (h->idx_bytes == 1) rc = mode == 0 ? launch_e_box<0, uint8_t>(h, L, out, B) : (mode == 1 ? launch_e_box<1, uint8_t>(h, L, out, B) : launch_e_box<2, uint8_t>(h, L, out, B));
+            else rc = mode == 0 ? launch_e_box<0, uint16_t>(h, L, out, B) : (mode == 1 ? launch_e_box<1, uint16_t>(h, L, out, B) : launch_e_box<2, uint16_t>(h, L, out, B));
+            if (rc) return rc;
+            lo = hi;
+        }
+    }
+    L.ex = h->g[0]; L.ey = h->g[1]; L.ez = h->g[2];   // everything pending now
+    if (int rc = launch_pml_on<1>(h, L, 0, nzl)) return rc;
+    return sample_probes(h, L, 0, nzl);
+}
+
 // 0 fast | 1 exact with exact reciprocals (every dx, cast to f32, is a power of two) | 2 exact with IEEE division
 int arithmetic_mode(fdtd_b200_handle h) {
     if (!(h->flags & FDTD_B200_EXACT_ARITHMETIC)) return 0;
@@ -490,6 +634,7 @@ int launch_h(fdtd_b200_handle h, int z_lo, int z_hi) {
     else if (h->idx_bytes == 1) rc = mode == 0 ? launch_h_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint8_t>(h, z_lo, z_hi) : launch_h_t<2, uint8_t>(h, z_lo, z_hi));
     else rc = mode == 0 ? launch_h_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_h_t<1, uint16_t>(h, z_lo, z_hi) : launch_h_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
+    if ((rc = launch_pml<0>(h, z_lo, z_hi))) return rc;
     return prof_end(h, 0);
 }
 int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
@@ -501,6 +646,7 @@ int launch_e(fdtd_b200_handle h, int z_lo, int z_hi) {
     else if (h->idx_bytes == 1) rc = mode == 0 ? launch_e_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint8_t>(h, z_lo, z_hi) : launch_e_t<2, uint8_t>(h, z_lo, z_hi));
     else rc = mode == 0 ? launch_e_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_e_t<1, uint16_t>(h, z_lo, z_hi) : launch_e_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
+    if ((rc = launch_pml<1>(h, z_lo, z_hi))) return rc;
     return prof_end(h, 1);
 }
 
@@ -521,6 +667,11 @@ int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi) {
     if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi));
     else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi));
     if (rc) return rc;
+    if (h->has_pml) {
+        if (z_lo != 0 || z_hi != static_cast<int>(h->nzl) || h->z_begin != 0 || h->z_end != h->nz)
+            return fail(h, FDTD_B200_ESTATE, "a fused step with a PML covers whole lattices only; z-slabs use the two-kernel path");
+        if ((rc = fused_pml_passes(h))) return rc;
+    }
     return prof_end(h, 0);
 }
 
@@ -797,6 +948,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_probe_slot) cudaFree(h->d_probe_slot);
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
     if (h->d_stage) cudaFree(h->d_stage);
+    for (int a = 0; a < 3; ++a) pml_free_axis(h, a);
     if (h->bstream) cudaStreamSynchronize(h->bstream);
     for (auto* link : {&h->lower, &h->upper}) { for (void* p : link->opened) cudaIpcCloseMemHandle(p); link->opened.clear(); }
     if (h->d_flags) cudaFree(h->d_flags);
@@ -823,6 +975,10 @@ int fdtd_b200_reset(fdtd_b200_handle h) {
         for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alt_alloc[c], 0, comp_floats * sizeof(float), h->stream));
     if (h->d_probe_ring)
         CU_TRY(h, cudaMemsetAsync(h->d_probe_ring, 0, sizeof(float) * 6 * h->n_probes_total * static_cast<size_t>(h->ring_steps), h->stream));
+    for (int a = 0; a < 3; ++a)
+        for (int fld = 0; fld < 2; ++fld)
+            for (int g = 0; g < 2; ++g)
+                if (h->pml[a].psi[fld][g]) CU_TRY(h, cudaMemsetAsync(h->pml[a].psi[fld][g], 0, h->pml[a].floats * sizeof(float), h->stream));
     h->n_src = 0; h->src_rows = 0; h->src_row = 0;
     h->tick = 0;
     h->time = 0.0;
@@ -868,6 +1024,104 @@ int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time) {
     h->probe_first_tick = tick;
     return FDTD_B200_OK;
 }
+
+// ---- CPML -------------------------------------------------------------------------------------------
+
+int fdtd_b200_pml_coefficients(double dt, const fdtd_b200_physical_constants* pc, double sigma, double kappa, double a, const double normal[3],
+                               double b_out[3], double c_out[3]) {
+    if (!pc || !normal || !b_out || !c_out) return fail(nullptr, FDTD_B200_EINVAL, "NULL argument");
+    const double e0 = pc->vacuum_permittivity;
+    const double b = std::exp(-((sigma / (e0 * kappa) + a / e0) * dt));   // CE 7.102 (pml.rs:44-47)
+    const double c = sigma * (b - 1.0) / (sigma * kappa + (kappa * kappa) * a);  // CE 7.99 (pml.rs:50)
+    for (int i = 0; i < 3; ++i) { b_out[i] = b * normal[i]; c_out[i] = c * normal[i]; }
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_pml_coefficients_graded(double dt, const fdtd_b200_physical_constants* pc, const fdtd_b200_graded_pml* g, double depth,
+                                      const double normal[3], double b_out[3], double c_out[3]) {
+    if (!g) return fail(nullptr, FDTD_B200_EINVAL, "NULL argument");
+    const double g1 = std::pow(depth, g->m);            // pml.rs:80-84
+    const double g2 = std::pow(1.0 - depth, g->m_a);
+    return fdtd_b200_pml_coefficients(dt, pc, g->sigma_max * g1, 1.0 + (g->kappa_max - 1.0) * g1, g->a_max * g2, normal, b_out, c_out);
+}
+
+int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const double* c_e, const double* b_h, const double* c_h) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (axis < 0 || axis > 2) return fail(h, FDTD_B200_EINVAL, "axis must be 0, 1 or 2");
+    if ((b_e == nullptr) != (c_e == nullptr) || (b_h == nullptr) != (c_h == nullptr) || (!b_e && b_h))
+        return fail(h, FDTD_B200_EINVAL, "pass b and c together (b_h/c_h optional, NULL = the E profile)");
+    if (h->p2p) return fail(h, FDTD_B200_ESTATE, "set the PML before connecting the peer-memory transport (which does not support it)");
+    if (h->fused && (h->z_begin != 0 || h->z_end != h->nz))
+        return fail(h, FDTD_B200_ESTATE, "a PML on z-slabs needs two-kernel handles (create them without FDTD_B200_FUSED_STEP)");
+    if (int rc = set_device(h)) return rc;
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    pml_free_axis(h, axis);
+    if (!b_e) return FDTD_B200_OK;  // cleared
+    if (!b_h) { b_h = b_e; c_h = c_e; }
+    const uint64_t ext = axis == 0 ? h->nx : (axis == 1 ? h->ny : h->nz);
+    const uint64_t lo = axis == 2 ? h->z_begin : 0, hi = axis == 2 ? h->z_end : ext;
+    auto& A = h->pml[axis];
+    std::vector<float2> bc_h, bc_e;
+    for (uint64_t i = 0; i < ext; ++i) {
+        if (!std::isfinite(b_e[i]) || !std::isfinite(c_e[i]) || !std::isfinite(b_h[i]) || !std::isfinite(c_h[i]))
+            return fail(h, FDTD_B200_EINVAL, "PML coefficients must be finite");
+        if ((c_e[i] == 0.0 && c_h[i] == 0.0) || i < lo || i >= hi) continue;
+        A.pos.push_back(static_cast<int>(i - lo));
+        A.h_active.push_back(c_h[i] != 0.0 ? 1 : 0);
+        bc_h.push_back(make_float2(static_cast<float>(b_h[i]), static_cast<float>(c_h[i])));
+        bc_e.push_back(make_float2(static_cast<float>(b_e[i]), static_cast<float>(c_e[i])));
+    }
+    A.n = static_cast<int>(A.pos.size());
+    if (A.n == 0) { A = fdtd_b200_solver::PmlAxis{}; return FDTD_B200_OK; }
+    A.floats = static_cast<size_t>(A.n) * (axis == 0 ? h->ny * h->nzl : (axis == 1 ? h->nx * h->nzl : h->nx * h->ny));
+    auto oom = [&](cudaError_t e) {
+        pml_free_axis(h, axis);
+        return fail(h, e == cudaErrorMemoryAllocation ? FDTD_B200_ENOMEM : FDTD_B200_ECUDA, std::string("PML allocation: ") + cudaGetErrorString(e));
+    };
+    cudaError_t e;
+    if ((e = cudaMalloc(&A.d_pos, sizeof(int) * A.n)) != cudaSuccess) return oom(e);
+    for (int k = 0; k < 2; ++k) if ((e = cudaMalloc(&A.d_bc[k], sizeof(float2) * A.n)) != cudaSuccess) return oom(e);
+    for (int fld = 0; fld < 2; ++fld)
+        for (int g = 0; g < 2; ++g) {
+            if ((e = cudaMalloc(&A.psi[fld][g], sizeof(float) * A.floats)) != cudaSuccess) return oom(e);
+            if ((e = cudaMemsetAsync(A.psi[fld][g], 0, sizeof(float) * A.floats, h->stream)) != cudaSuccess) return oom(e);
+        }
+    if ((e = cudaMemcpyAsync(A.d_pos, A.pos.data(), sizeof(int) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if ((e = cudaMemcpyAsync(A.d_bc[0], bc_h.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if ((e = cudaMemcpyAsync(A.d_bc[1], bc_e.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return oom(e);   // the host vectors go out of scope
+    h->has_pml = true;
+    return FDTD_B200_OK;
+}
+
+int fdtd_b200_has_pml(fdtd_b200_handle h) { return h && h->has_pml ? 1 : 0; }
+
+uint64_t fdtd_b200_pml_state_floats(fdtd_b200_handle h) {
+    if (!h) return 0;
+    uint64_t n = 0;
+    for (int a = 0; a < 3; ++a) n += 4 * static_cast<uint64_t>(h->pml[a].floats);
+    return n;
+}
+
+// ψ arrays in the order axis x, y, z × (H: G_ab, G_ac; E: G_ab, G_ac)
+static int pml_state_copy(fdtd_b200_handle h, float* host, bool to_host) {
+    if (!h || (!host && fdtd_b200_pml_state_floats(h))) return fail(h, FDTD_B200_EINVAL, "NULL argument");
+    if (int rc = set_device(h)) return rc;
+    size_t off = 0;
+    for (int a = 0; a < 3; ++a)
+        for (int fld = 0; fld < 2; ++fld)
+            for (int g = 0; g < 2; ++g) {
+                const auto& A = h->pml[a];
+                if (!A.floats) continue;
+                if (to_host) CU_TRY(h, cudaMemcpyAsync(host + off, A.psi[fld][g], sizeof(float) * A.floats, cudaMemcpyDeviceToHost, h->stream));
+                else CU_TRY(h, cudaMemcpyAsync(A.psi[fld][g], host + off, sizeof(float) * A.floats, cudaMemcpyHostToDevice, h->stream));
+                off += A.floats;
+            }
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return FDTD_B200_OK;
+}
+int fdtd_b200_read_pml_state(fdtd_b200_handle h, float* out) { return pml_state_copy(h, out, true); }
+int fdtd_b200_write_pml_state(fdtd_b200_handle h, const float* in) { return pml_state_copy(h, const_cast<float*>(in), false); }
 
 uint64_t fdtd_b200_tick(fdtd_b200_handle h) { return h ? h->tick : 0; }
 double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
@@ -1573,6 +1827,7 @@ int fdtd_b200_p2p_connected(fdtd_b200_handle h) { return h && h->p2p ? 1 : 0; }
 int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob) {
     if (!h || !blob) return fail(h, FDTD_B200_EINVAL, "NULL argument");
     if (!h->fused) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport needs a fused-step handle (FDTD_B200_FUSED_STEP on an eligible lattice)");
+    if (h->has_pml) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport does not run the PML passes; use the two-kernel slab path");
     if (int rc = set_device(h)) return rc;
     if (!h->d_flags) {
         CU_TRY(h, cudaMalloc(&h->d_flags, 64));

@@ -218,22 +218,24 @@ def save_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
     state.sync()
     tmp = path + ".tmp"
     with open(tmp, "wb") as f:
-        f.write(_MAGIC + struct.pack("<6QQd", nx, ny, state.lattice[2], zb, ze, 0, state.tick(), state.time()))
+        psi = state.read_pml_state()   # CPML ψ arrays (empty without a PML)
+        f.write(_MAGIC + struct.pack("<6QQd", nx, ny, state.lattice[2], zb, ze, psi.size, state.tick(), state.time()))
         for comp in (FieldComponent.E, FieldComponent.H):
             for z in range(zb, ze, planes_per_chunk):
                 z1 = min(z + planes_per_chunk, ze)
                 f.write(state.read_field(comp, (0, 0, z), (nx, ny, z1)).tobytes())
+        f.write(psi.tobytes())
     os.replace(tmp, path)
 
 
 def load_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
-    """Restores fields, tick and time into a state created for the same lattice/slab (materials, sources and probes belong
-    to the instance and are not part of the checkpoint).  Slab-decomposed runs refresh their halos afterwards."""
+    """Restores fields, tick and time into a state created for the same lattice/slab (materials, PML profiles, sources and probes
+    belong to the instance and are not part of the checkpoint; the PML's ψ state is).  Slab-decomposed runs refresh their halos afterwards."""
     nx, ny, nz = state.lattice
     with open(path, "rb") as f:
         if f.read(len(_MAGIC)) != _MAGIC:
             raise ValueError(f"{path}: not a fdtd_b200 checkpoint")
-        hx, hy, hz, zb, ze, _, tick, time = struct.unpack("<6QQd", f.read(64))
+        hx, hy, hz, zb, ze, n_psi, tick, time = struct.unpack("<6QQd", f.read(64))
         if (hx, hy, hz, zb, ze) != (nx, ny, nz, state.z_begin, state.z_end):
             raise ValueError(f"{path}: checkpoint of lattice {(hx, hy, hz)} slab {(zb, ze)} does not match this state")
         for comp in (FieldComponent.E, FieldComponent.H):
@@ -244,4 +246,8 @@ def load_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
                 if buf.size != n:
                     raise ValueError(f"{path}: truncated checkpoint")
                 state.write_field(comp, buf, (0, 0, z), (nx, ny, z1))
+        if n_psi != state.read_pml_state().size:
+            raise ValueError(f"{path}: checkpoint carries {n_psi} ψ values, this state's PML has {state.read_pml_state().size}")
+        if n_psi:
+            state.write_pml_state(np.frombuffer(f.read(4 * n_psi), dtype=np.float32))
     state.set_time(int(tick), float(time))

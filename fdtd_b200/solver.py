@@ -150,9 +150,115 @@ class WithAmplitudes:
         return SourceValues(tuple(a * v for a in self.amplitude.j), tuple(a * v for a in self.amplitude.m))
 
 
+@dataclass(frozen=True)
+class GradedPml:
+    """cem-solver/src/fdtd/pml.rs:13-20"""
+    m: float = 3.0
+    m_a: float = 1.0
+    sigma_max: float = 2.5
+    kappa_max: float = 1.0
+    a_max: float = 0.1
+    normal: tuple = (1.0, 0.0, 0.0)
+
+
+@dataclass(frozen=True)
+class PmlCoefficients:
+    """cem-solver/src/fdtd/pml.rs:27-86: the scalar (b, c) of CE 7.102 / 7.99 times the `normal` the caller passes."""
+    b: tuple
+    c: tuple
+
+    @staticmethod
+    def new(resolution: "Resolution", physical_constants: "PhysicalConstants", sigma: float, kappa: float, a: float, normal) -> "PmlCoefficients":
+        pc = L.PhysicalConstants(physical_constants.vacuum_permittivity, physical_constants.vacuum_permeability)
+        n = (C.c_double * 3)(*normal)
+        b, c = (C.c_double * 3)(), (C.c_double * 3)()
+        L.check(L.lib().fdtd_b200_pml_coefficients(resolution.temporal, C.byref(pc), sigma, kappa, a, n, b, c))
+        return PmlCoefficients(tuple(b), tuple(c))
+
+    @staticmethod
+    def new_graded(resolution: "Resolution", physical_constants: "PhysicalConstants", m: float, m_a: float, sigma_max: float, kappa_max: float,
+                   a_max: float, depth: float, normal) -> "PmlCoefficients":
+        pc = L.PhysicalConstants(physical_constants.vacuum_permittivity, physical_constants.vacuum_permeability)
+        g = L.GradedPml(m, m_a, sigma_max, kappa_max, a_max)
+        n = (C.c_double * 3)(*normal)
+        b, c = (C.c_double * 3)(), (C.c_double * 3)()
+        L.check(L.lib().fdtd_b200_pml_coefficients_graded(resolution.temporal, C.byref(pc), C.byref(g), depth, n, b, c))
+        return PmlCoefficients(tuple(b), tuple(c))
+
+
+class PmlProfiles:
+    """Separable PML in the form the C ABI takes (fdtd_b200_set_pml): per axis the (b, c) of the E half-step and of the
+    H half-step over the global coordinate along that axis.  `None` for an axis = no PML along it."""
+
+    def __init__(self, lattice: Sequence[int]):
+        self.lattice = tuple(int(v) for v in lattice)
+        self.axes = [None, None, None]   # (b_e, c_e, b_h, c_h) float64 arrays
+
+    def set_axis(self, axis: int, b_e, c_e, b_h=None, c_h=None) -> "PmlProfiles":
+        n = self.lattice[axis]
+        arrs = [np.ascontiguousarray(v, dtype=np.float64) for v in (b_e, c_e, b_e if b_h is None else b_h, c_e if c_h is None else c_h)]
+        if any(a.shape != (n,) for a in arrs):
+            raise ValueError(f"PML profiles of axis {axis} must have {n} entries")
+        self.axes[axis] = tuple(arrs)
+        return self
+
+    def any(self) -> bool:
+        return any(a is not None and (np.any(a[1] != 0) or np.any(a[3] != 0)) for a in self.axes)
+
+    @staticmethod
+    def graded(config: "FdtdSolverConfig", thickness: int, pml: GradedPml = GradedPml(), axes: Sequence[int] = (0, 1, 2),
+               staggered: bool = True) -> "PmlProfiles":
+        """`thickness` PML cells on both faces of each axis, graded with `PmlCoefficients::new_graded` over the normalised
+        depth.  On this lattice H[i] sits half a cell below E[i] (backward differences, cpu/mod.rs:431-443), so with
+        `staggered` the H profile is evaluated at i − ½; staggered=False is the reference's one-set-per-cell model."""
+        n = config.lattice_size()
+        out = PmlProfiles(n)
+        for a in axes:
+            t = min(int(thickness), max((n[a] - 1) // 2, 0))
+            if t <= 0:
+                continue
+            prof = [np.zeros(n[a]) for _ in range(4)]
+            hi_if = n[a] - 1 - t
+            for i in range(n[a]):
+                for (bi, ci, off) in ((0, 1, 0.0), (2, 3, -0.5 if staggered else 0.0)):
+                    pos = i + off
+                    d = max((t - pos) / t if pos < t else 0.0, (pos - hi_if) / t if pos > hi_if else 0.0)
+                    d = min(d, 1.0)
+                    if d > 0.0:
+                        co = PmlCoefficients.new_graded(config.resolution, config.physical_constants, pml.m, pml.m_a, pml.sigma_max,
+                                                        pml.kappa_max, pml.a_max, d, (1.0, 0.0, 0.0))
+                        prof[bi][i], prof[ci][i] = co.b[0], co.c[0]
+            out.set_axis(a, *prof)
+        return out
+
+    @staticmethod
+    def from_cells(lattice: Sequence[int], cells: dict) -> "PmlProfiles":
+        """Per-cell `Option<PmlCoefficients>` answers ({point: PmlCoefficients}, the reference's `pml(point)` callback,
+        cpu/mod.rs:242-255) → per-axis profiles.  The coefficient of axis a must depend on the coordinate along a only;
+        where a cell has none for an axis that another cell at the same coordinate has, the non-zero one is used (the
+        reference's "todo: merge pmls present at this point", runner.rs:672).  The application passes −normal
+        (runner.rs:667), which flips the sign of b and c on three faces: the magnitudes are used (b ≥ 0, c ≤ 0)."""
+        out = PmlProfiles(lattice)
+        prof = [[np.zeros(n), np.zeros(n)] for n in out.lattice]
+        for point, co in cells.items():
+            for a in range(3):
+                b, c = abs(float(co.b[a])), -abs(float(co.c[a]))
+                if c == 0.0:
+                    continue
+                i = int(point[a])
+                if prof[a][1][i] != 0.0 and (prof[a][0][i] != b or prof[a][1][i] != c):
+                    raise ValueError(f"PML is not separable: axis {a} coordinate {i} has two different coefficient sets")
+                prof[a][0][i], prof[a][1][i] = b, c
+        for a in range(3):
+            if np.any(prof[a][1] != 0):
+                out.set_axis(a, prof[a][0], prof[a][1])
+        return out
+
+
 class DomainDescription:
-    """cem-solver/src/lib.rs:60-67: per-point material callback.  `pml` is accepted and ignored exactly as
-    the reference's update ignores it (cpu/mod.rs:424-425 "todo: use pml")."""
+    """cem-solver/src/lib.rs:60-67: per-point material callback and per-point `pml` callback.  The reference stores the
+    PML answers and never uses them (cpu/mod.rs:424-425 "todo: use pml"); this engine runs the CPML recursion with them
+    (parity unpinned) — return None everywhere (the default) for the reference's executed behaviour."""
 
     def material(self, point: Point) -> Material:  # pragma: no cover - interface
         raise NotImplementedError
@@ -165,9 +271,10 @@ class MaterialLattice(DomainDescription):
     """A pre-rasterised domain: palette + per-cell id lattice ([nz, ny, nx] or flat, x fastest).  This is the
     form the C ABI takes (the per-cell callback is the reference's construction bottleneck)."""
 
-    def __init__(self, palette: Sequence[Material], ids: Optional[np.ndarray] = None):
+    def __init__(self, palette: Sequence[Material], ids: Optional[np.ndarray] = None, pml: Optional["PmlProfiles"] = None):
         self.palette = list(palette)
         self.ids = None if ids is None else np.ascontiguousarray(np.asarray(ids).reshape(-1), dtype=np.uint32)
+        self.pml_profiles = pml
 
     def material(self, point: Point) -> Material:
         raise TypeError("MaterialLattice is consumed whole by create_instance")
@@ -217,6 +324,7 @@ class FdtdB200Backend:
             # scene.SceneDomain: rasterised on the device when the state is created — no host lattice, no per-cell callback
             inst = FdtdB200SolverInstance(self, config, domain_description.palette, None)
             inst.scene = domain_description
+            inst.pml = getattr(domain_description, "pml_profiles", None)
             return inst
         if isinstance(domain_description, MaterialLattice):
             palette = domain_description.palette
@@ -231,10 +339,13 @@ class FdtdB200Backend:
             cells = n[0] * n[1] * (ze - zb)
             mats = (L.Material * cells)()
             i = 0
+            pml_cells = {}
             for z in range(zb, ze):
                 for y in range(n[1]):
                     for x in range(n[0]):
-                        domain_description.pml((x, y, z))
+                        co = domain_description.pml((x, y, z))
+                        if co is not None:
+                            pml_cells[(x, y, z)] = co
                         m = domain_description.material((x, y, z))
                         mats[i] = L.Material(*m.as_row())
                         i += 1
@@ -244,7 +355,13 @@ class FdtdB200Backend:
             L.check(lib.fdtd_b200_index_materials(mats, cells, ids.ctypes.data_as(C.POINTER(C.c_uint32)), pal, 65536, C.byref(npal)))
             palette = [Material(p.relative_permeability, p.magnetic_conductivity, p.relative_permittivity, p.eletrical_conductivity)
                        for p in pal[: npal.value]]
-        return FdtdB200SolverInstance(self, config, palette, ids)
+            inst = FdtdB200SolverInstance(self, config, palette, ids)
+            if pml_cells:
+                inst.pml = PmlProfiles.from_cells(n, pml_cells)
+            return inst
+        inst = FdtdB200SolverInstance(self, config, palette, ids)
+        inst.pml = getattr(domain_description, "pml_profiles", None)
+        return inst
 
 
 class FdtdB200SolverInstance:
@@ -257,6 +374,7 @@ class FdtdB200SolverInstance:
         self.palette = list(palette)
         self.ids = ids
         self.scene = None
+        self.pml: Optional[PmlProfiles] = None
         self.lattice = config.lattice_size()
 
     # -- SolverInstance -------------------------------------------------------------------------
@@ -272,6 +390,8 @@ class FdtdB200SolverInstance:
         if self.scene is not None:
             sc = self.scene
             L.check(lib.fdtd_b200_set_materials_from_scene(handle, sc.c_transform(), sc.c_shapes(), len(sc.shapes), 0), handle)
+        if self.pml is not None and self.pml.any():
+            state.set_pml(self.pml)
         return state
 
     def begin_update(self, state: "FdtdB200SolverState") -> "FdtdB200UpdatePass":
@@ -322,6 +442,30 @@ class FdtdB200SolverState:
 
     def set_time(self, tick: int, time: float) -> None:
         L.check(self._lib.fdtd_b200_set_time(self._h, int(tick), float(time)), self._h)
+
+    # CPML (include/fdtd_b200.h "CPML")
+    def set_pml(self, profiles: Optional[PmlProfiles]) -> None:
+        dp = C.POINTER(C.c_double)
+        for a in range(3):
+            ax = None if profiles is None else profiles.axes[a]
+            if ax is None:
+                L.check(self._lib.fdtd_b200_set_pml(self._h, a, None, None, None, None), self._h)
+            else:
+                L.check(self._lib.fdtd_b200_set_pml(self._h, a, *[v.ctypes.data_as(dp) for v in ax]), self._h)
+
+    def has_pml(self) -> bool:
+        return bool(self._lib.fdtd_b200_has_pml(self._h))
+
+    def read_pml_state(self) -> np.ndarray:
+        out = np.zeros(int(self._lib.fdtd_b200_pml_state_floats(self._h)), dtype=np.float32)
+        L.check(self._lib.fdtd_b200_read_pml_state(self._h, out.ctypes.data_as(C.POINTER(C.c_float))), self._h)
+        return out
+
+    def write_pml_state(self, values: np.ndarray) -> None:
+        v = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
+        if v.size != int(self._lib.fdtd_b200_pml_state_floats(self._h)):
+            raise ValueError("ψ state does not match this handle's PML")
+        L.check(self._lib.fdtd_b200_write_pml_state(self._h, v.ctypes.data_as(C.POINTER(C.c_float))), self._h)
 
     # batched API
     def cell_index(self, point: Point) -> int:

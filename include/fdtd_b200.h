@@ -168,6 +168,35 @@ double fdtd_b200_time(fdtd_b200_handle h);
  * rows and restarts the probe ring at `tick`. */
 int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time);
 
+/* ---- CPML ------------------------------------------------------------------------
+ * The reference computes PML coefficients (fdtd/pml.rs:34-86), keeps a per-cell indirection + ψ storage
+ * (cpu/mod.rs:242-255, 649-679) and never runs the recursion (`psi = zeros`, cpu/mod.rs:419-425, 454, 498): parity unpinned.
+ * Here the recursion runs, for separable PMLs: per axis a profile (b[i], c[i]) over the GLOBAL coordinate along that axis,
+ * one for the E half-step and one for the H half-step (half a cell apart on the Yee grid; the reference has one
+ * `PmlCoefficients` per cell for both — pass NULL for b_h/c_h to get that).  Cells whose c is non-zero on an axis carry two
+ * ψ values per half-step for that axis; psi = ±curl(G_x, G_y, G_z) enters the update where the reference has its `+ psi`. */
+
+/* cem-solver/src/fdtd/pml.rs:13-20 without the normal. */
+typedef struct fdtd_b200_graded_pml {
+    double m, m_a, sigma_max, kappa_max, a_max;
+} fdtd_b200_graded_pml;
+
+/* `PmlCoefficients::new` (pml.rs:34-56): scalar b, c times `normal` (host, f64). */
+int fdtd_b200_pml_coefficients(double dt, const fdtd_b200_physical_constants* constants, double sigma, double kappa, double a,
+                               const double normal[3], double b_out[3], double c_out[3]);
+/* `PmlCoefficients::new_graded` (pml.rs:58-86); depth in [0, 1]. */
+int fdtd_b200_pml_coefficients_graded(double dt, const fdtd_b200_physical_constants* constants, const fdtd_b200_graded_pml* g, double depth,
+                                      const double normal[3], double b_out[3], double c_out[3]);
+/* Profiles of one axis (arrays of the global extent of that axis); b_e == NULL clears the axis.  ψ starts at zero.
+ * Fused-step handles run the PML as extra passes after the fused kernel (whole lattices only); z-slab handles must be
+ * two-kernel handles; not available with the peer-memory transport. */
+int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const double* c_e, const double* b_h, const double* c_h);
+int fdtd_b200_has_pml(fdtd_b200_handle h);
+/* ψ state for checkpoints: all ψ arrays of this handle, concatenated. */
+uint64_t fdtd_b200_pml_state_floats(fdtd_b200_handle h);
+int fdtd_b200_read_pml_state(fdtd_b200_handle h, float* out);
+int fdtd_b200_write_pml_state(fdtd_b200_handle h, const float* in);
+
 /* Introspection used by tests and the bench. */
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
 int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */

@@ -65,6 +65,10 @@ def _load(fast: bool) -> C.CDLL:
     lib.fdtd_ref_set_materials.restype = C.c_int
     lib.fdtd_ref_set_materials.argtypes = [C.c_void_p, dp, C.c_uint32, C.POINTER(C.c_uint32), C.c_double, C.c_double]
     lib.fdtd_ref_update_coefficients.argtypes = [C.c_double, C.c_double, C.c_double, dp, dp]
+    lib.fdtd_ref_pml_coefficients.argtypes = [C.c_double] * 6 + [dp, dp]
+    lib.fdtd_ref_pml_coefficients_graded.argtypes = [C.c_double] * 9 + [dp, dp]
+    lib.fdtd_ref_set_pml.restype = C.c_int
+    lib.fdtd_ref_set_pml.argtypes = [C.c_void_p, C.c_uint64, u64p, dp, dp]
     lib.fdtd_ref_reset.argtypes = [C.c_void_p]
     lib.fdtd_ref_begin_update.argtypes = [C.c_void_p]
     lib.fdtd_ref_set_forcing.restype = C.c_int
@@ -117,6 +121,24 @@ def update_coefficients(dt: float, eps0: float, mu0: float, material) -> np.ndar
     out = np.zeros(4, dtype=np.float64)
     _load(False).fdtd_ref_update_coefficients(dt, eps0, mu0, _p(m, C.c_double), _p(out, C.c_double))
     return out
+
+
+def pml_coefficients(dt: float, eps0: float, mu0: float, sigma: float, kappa: float, a: float, normal) -> tuple[np.ndarray, np.ndarray]:
+    """`PmlCoefficients::new` (pml.rs:34-56): (b[3], c[3]) = scalar b, c times `normal`."""
+    n = np.ascontiguousarray(normal, dtype=np.float64)
+    out = np.zeros(6, dtype=np.float64)
+    _load(False).fdtd_ref_pml_coefficients(dt, eps0, mu0, sigma, kappa, a, _p(n, C.c_double), _p(out, C.c_double))
+    return out[:3].copy(), out[3:].copy()
+
+
+def pml_coefficients_graded(dt: float, eps0: float, mu0: float, m: float, m_a: float, sigma_max: float, kappa_max: float, a_max: float,
+                            depth: float, normal) -> tuple[np.ndarray, np.ndarray]:
+    """`PmlCoefficients::new_graded` (pml.rs:58-86)."""
+    n = np.ascontiguousarray(normal, dtype=np.float64)
+    out = np.zeros(6, dtype=np.float64)
+    _load(False).fdtd_ref_pml_coefficients_graded(dt, eps0, mu0, m, m_a, sigma_max, kappa_max, a_max, depth, _p(n, C.c_double),
+                                                  _p(out, C.c_double))
+    return out[:3].copy(), out[3:].copy()
 
 
 def iter_points(start, end) -> np.ndarray:
@@ -188,6 +210,43 @@ class RefSolver:
         rc = self._lib.fdtd_ref_set_materials(self._h, _p(pal, C.c_double), pal.shape[0], idp, eps0, mu0)
         if rc:
             raise ValueError(f"fdtd_ref_set_materials rc={rc}")
+
+    def set_pml(self, cells, b, c, b_h=None, c_h=None) -> None:
+        """Per-cell `PmlCoefficients` (cells: linear indices, b/c: [n, 3]) — the cells whose `pml(point)` is Some.
+        b_h/c_h: a second set used by the H half-step (half-cell staggered grading); None = one set, the reference's model."""
+        cc = _u64(cells).reshape(-1)
+
+        def pack(bb, cv):
+            out = np.ascontiguousarray(np.concatenate([np.asarray(bb, dtype=np.float64).reshape(-1, 3),
+                                                       np.asarray(cv, dtype=np.float64).reshape(-1, 3)], axis=1))
+            assert out.shape[0] == cc.size
+            return out
+
+        bc = pack(b, c)
+        bch = pack(b_h, c_h) if b_h is not None else None
+        if self._lib.fdtd_ref_set_pml(self._h, cc.size, _p(cc, C.c_uint64), _p(bc, C.c_double), _p(bch, C.c_double) if bch is not None else None):
+            raise IndexError("set_pml: cell outside the lattice")
+
+    def set_pml_profiles(self, b_axes, c_axes, b_axes_h=None, c_axes_h=None) -> None:
+        """Separable PML: per-axis profiles b_axes[a][i], c_axes[a][i] (E half-step) and optionally *_h (H half-step);
+        every cell with a non-zero c on some axis in either set is a PML cell."""
+        nx, ny, nz = self.size
+        if b_axes_h is None:
+            b_axes_h, c_axes_h = b_axes, c_axes
+        z, y, x = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+        sets = []
+        for bs, cs in ((b_axes, c_axes), (b_axes_h, c_axes_h)):
+            bx, by, bz = (np.asarray(v, dtype=np.float64) for v in bs)
+            cx, cy, cz = (np.asarray(v, dtype=np.float64) for v in cs)
+            sets.append((bx, by, bz, cx, cy, cz))
+        on = np.zeros(x.shape, dtype=bool)
+        for (_, _, _, cx, cy, cz) in sets:
+            on |= (cx[x] != 0) | (cy[y] != 0) | (cz[z] != 0)
+        cells = ((z * ny + y) * nx + x)[on]
+        packed = []
+        for (bx, by, bz, cx, cy, cz) in sets:
+            packed.append((np.stack([bx[x[on]], by[y[on]], bz[z[on]]], axis=1), np.stack([cx[x[on]], cy[y[on]], cz[z[on]]], axis=1)))
+        self.set_pml(cells, packed[0][0], packed[0][1], packed[1][0], packed[1][1])
 
     def reset(self) -> None:
         self._lib.fdtd_ref_reset(self._h)

@@ -149,6 +149,30 @@ inline double continous_wave(double time, double phase, double frequency) {
     return std::cos(TAU * frequency * time + phase);
 }
 
+// cem-solver/src/fdtd/pml.rs:27-86.  `PmlCoefficients { b, c }`: the scalar b (CE 7.102) and c (CE 7.99) times the
+// `normal` vector the caller passes (the application passes −GradedPml.normal, runner.rs:667 — signed).
+struct PmlCoefficients {
+    double b[3] = {0, 0, 0};
+    double c[3] = {0, 0, 0};
+};
+
+inline PmlCoefficients pml_coefficients_new(const Resolution& r, const PhysicalConstants& pc, double sigma, double kappa, double a,
+                                            const double normal[3]) {
+    const double b = std::exp(-((sigma / (pc.vacuum_permittivity * kappa) + a / pc.vacuum_permittivity) * r.temporal));
+    const double c = sigma * (b - 1.0) / (sigma * kappa + (kappa * kappa) * a);  // kappa.powi(2)
+    PmlCoefficients out;
+    for (int i = 0; i < 3; ++i) { out.b[i] = b * normal[i]; out.c[i] = c * normal[i]; }
+    return out;
+}
+
+// pml.rs:58-86: g1 = depth^m, g2 = (1−depth)^m_a, σ = σmax·g1, κ = 1 + (κmax−1)·g1, a = amax·g2.
+inline PmlCoefficients pml_coefficients_new_graded(const Resolution& r, const PhysicalConstants& pc, double m, double m_a, double sigma_max,
+                                                   double kappa_max, double a_max, double depth, const double normal[3]) {
+    const double g1 = std::pow(depth, m);
+    const double g2 = std::pow(1.0 - depth, m_a);
+    return pml_coefficients_new(r, pc, sigma_max * g1, 1.0 + (kappa_max - 1.0) * g1, a_max * g2, normal);
+}
+
 template <class T>
 class Solver {
 public:
@@ -166,6 +190,51 @@ public:
     std::vector<SourceSlot> source_buffer;        // slot 0 = dummy (cpu/mod.rs:380-381)
     size_t tick = 0;
     double time = 0.0;
+
+    // CPML.  The reference builds this storage (cpu/mod.rs:242-255 `PmlInstance{indirection, coefficients}`,
+    // :649-679 `PmlState{psi_e, psi_h}`, entry 0 = "all non-pml cells") but never runs the recursion (`psi = zeros`,
+    // cpu/mod.rs:419-425, 454, 498).  Here it is run, parity unpinned: per PML cell and derivative axis a the auxiliary vector
+    //   G_a ← b_a·G_a + c_a·∂F/∂x_a            (CE 7.98/7.105 recursive convolution, coefficients of pml.rs),
+    // and the term the reference's update already has a slot for is psi = ±curl(G_x, G_y, G_z) — the matrix form of the
+    // commented-out `psi_total` (pml.rs:89-92): + for the E half-step, − for the H half-step (which subtracts the curl).
+    struct PmlCell { T b[3], c[3], bh[3], ch[3]; };  // E half-step uses (b, c), H half-step (bh, ch); the reference has one set for both
+    struct PsiCell { Vec3<T> g[3]; };
+    std::vector<uint32_t> pml_indirection;   // per lattice cell, 0 = not a PML cell
+    std::vector<PmlCell> pml_cells;          // entry 0 = dummy
+    std::vector<PsiCell> psi_e, psi_h;
+
+    void set_pml(size_t index, const PmlCoefficients& p) { set_pml(index, p, p); }
+    void set_pml(size_t index, const PmlCoefficients& p, const PmlCoefficients& ph) {
+        if (pml_indirection.empty()) {
+            pml_indirection.assign(strider.len(), 0u);
+            pml_cells.assign(1, PmlCell{});
+        }
+        PmlCell cell;
+        for (int i = 0; i < 3; ++i) {
+            cell.b[i] = static_cast<T>(p.b[i]); cell.c[i] = static_cast<T>(p.c[i]);
+            cell.bh[i] = static_cast<T>(ph.b[i]); cell.ch[i] = static_cast<T>(ph.c[i]);
+        }
+        if (pml_indirection[index] == 0) {
+            pml_indirection[index] = static_cast<uint32_t>(pml_cells.size());
+            pml_cells.push_back(cell);
+        } else {
+            pml_cells[pml_indirection[index]] = cell;
+        }
+        psi_e.resize(pml_cells.size());
+        psi_h.resize(pml_cells.size());
+    }
+
+    // returns curl(G_x, G_y, G_z) after advancing the recursion of PML cell `k`
+    Vec3<T> advance_psi(std::vector<PsiCell>& psi, bool h_step, uint32_t k, const Vec3<T>& ddx, const Vec3<T>& ddy, const Vec3<T>& ddz) {
+        const PmlCell& p = pml_cells[k];
+        const T* b = h_step ? p.bh : p.b;
+        const T* c = h_step ? p.ch : p.c;
+        PsiCell& s = psi[k];
+        s.g[0] = b[0] * s.g[0] + c[0] * ddx;
+        s.g[1] = b[1] * s.g[1] + c[1] * ddy;
+        s.g[2] = b[2] * s.g[2] + c[2] * ddz;
+        return curl(s.g[0], s.g[1], s.g[2]);
+    }
 
     Solver(const size_t n[3], const Resolution& res) : strider(n), dt(res.temporal) {
         for (int i = 0; i < 3; ++i) resolution[i] = static_cast<T>(res.spatial[i]);
@@ -187,6 +256,8 @@ public:
         }
         std::fill(source_field.begin(), source_field.end(), size_t(0));
         source_buffer.clear();
+        std::fill(psi_e.begin(), psi_e.end(), PsiCell{});
+        std::fill(psi_h.begin(), psi_h.end(), PsiCell{});
         tick = 0;
         time = 0.0;
     }
@@ -248,7 +319,7 @@ public:
         const int previous = static_cast<int>(tick % 2);  // SwapBufferIndex::from_tick
         const int next = (previous + 1) % 2;
         const long long len = static_cast<long long>(strider.len());
-        const Vec3<T> psi{};  // "todo: use pml" — zero in the reference
+        const bool has_pml = !pml_indirection.empty();  // without PML cells psi is zero, as the reference executes it
 
         {
             const auto& e_prev = e_field[previous];
@@ -266,6 +337,8 @@ public:
                 Vec3<T> m_source{};
                 if (sid != 0) m_source = source_buffer[sid].m;
                 const Coeff& c = coeffs[i];
+                Vec3<T> psi{};
+                if (has_pml && pml_indirection[i] != 0) psi = -advance_psi(psi_h, true, pml_indirection[i], ddx, ddy, ddz);
                 h_next[i] = c.d_a * h_prev[i] + c.d_b * (-e_curl - m_source + psi);
             }
         }
@@ -285,6 +358,8 @@ public:
                 Vec3<T> j_source{};
                 if (sid != 0) j_source = source_buffer[sid].j;
                 const Coeff& c = coeffs[i];
+                Vec3<T> psi{};
+                if (has_pml && pml_indirection[i] != 0) psi = advance_psi(psi_e, false, pml_indirection[i], ddx, ddy, ddz);
                 e_next[i] = c.c_a * e_prev[i] + c.c_b * (h_curl - j_source + psi);
             }
         }

@@ -85,6 +85,35 @@ void fdtd_ref_update_coefficients(double dt, double eps0, double mu0, const doub
     out[0] = u.c_a; out[1] = u.c_b; out[2] = u.d_a; out[3] = u.d_b;
 }
 
+// pml.rs:34-86.  out: b[3], c[3].
+void fdtd_ref_pml_coefficients(double dt, double eps0, double mu0, double sigma, double kappa, double a, const double normal[3], double out[6]) {
+    Resolution r{{0, 0, 0}, dt};
+    const PmlCoefficients p = pml_coefficients_new(r, PhysicalConstants{eps0, mu0}, sigma, kappa, a, normal);
+    for (int i = 0; i < 3; ++i) { out[i] = p.b[i]; out[3 + i] = p.c[i]; }
+}
+void fdtd_ref_pml_coefficients_graded(double dt, double eps0, double mu0, double m, double m_a, double sigma_max, double kappa_max, double a_max,
+                                      double depth, const double normal[3], double out[6]) {
+    Resolution r{{0, 0, 0}, dt};
+    const PmlCoefficients p = pml_coefficients_new_graded(r, PhysicalConstants{eps0, mu0}, m, m_a, sigma_max, kappa_max, a_max, depth, normal);
+    for (int i = 0; i < 3; ++i) { out[i] = p.b[i]; out[3 + i] = p.c[i]; }
+}
+
+// cpu/mod.rs:242-255: the instance asks `pml(point)` for every cell; here the caller passes the cells that answered Some.
+// cells: linear indices; bc: [n][6] = b xyz, c xyz; bc_h: the same for the H half-step (NULL = the reference's model: one set).
+int fdtd_ref_set_pml(void* h, uint64_t n, const uint64_t* cells, const double* bc, const double* bc_h) {
+    return visit(static_cast<Any*>(h), [&](auto& s) {
+        for (uint64_t k = 0; k < n; ++k) {
+            if (cells[k] >= s.strider.len()) return 1;
+            PmlCoefficients p;
+            for (int i = 0; i < 3; ++i) { p.b[i] = bc[6 * k + i]; p.c[i] = bc[6 * k + 3 + i]; }
+            PmlCoefficients ph = p;
+            if (bc_h) for (int i = 0; i < 3; ++i) { ph.b[i] = bc_h[6 * k + i]; ph.c[i] = bc_h[6 * k + 3 + i]; }
+            s.set_pml(static_cast<size_t>(cells[k]), p, ph);
+        }
+        return 0;
+    });
+}
+
 void fdtd_ref_reset(void* h) { visit(static_cast<Any*>(h), [](auto& s) { s.reset_state(); return 0; }); }
 void fdtd_ref_begin_update(void* h) { visit(static_cast<Any*>(h), [](auto& s) { s.begin_update(); return 0; }); }
 int fdtd_ref_set_forcing(void* h, const uint64_t point[3], const double j[3], const double m[3]) {

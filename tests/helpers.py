@@ -16,6 +16,10 @@ def oracle_run(oracle, w, n_steps: int, precision: int, init=None, probes=None, 
     """Returns (solver, probe_series).  init = (E0, H0) arrays [nz,ny,nx,3] or None."""
     s = oracle.RefSolver(w.lattice, w.resolution.spatial, w.resolution.temporal, precision=precision, fast=fast)
     s.set_materials(w.palette_rows(), w.ids, w.constants.vacuum_permittivity, w.constants.vacuum_permeability)
+    if getattr(w, "pml", None) is not None and w.pml.any():
+        n = w.lattice
+        ax = [a if a is not None else (np.zeros(n[k]),) * 4 for k, a in enumerate(w.pml.axes)]
+        s.set_pml_profiles([a[0] for a in ax], [a[1] for a in ax], [a[2] for a in ax], [a[3] for a in ax])
     if init is not None:
         s.write_field(oracle.E, init[0])
         s.write_field(oracle.H, init[1])
@@ -25,14 +29,14 @@ def oracle_run(oracle, w, n_steps: int, precision: int, init=None, probes=None, 
     return s, series
 
 
-def b200_state(b200, w, exact: bool = False, generic: bool = False, z_slab=None, device: int = 0):
-    backend = b200.FdtdB200Backend(device=device, exact_arithmetic=exact, force_generic_kernels=generic, z_slab=z_slab)
+def b200_state(b200, w, exact: bool = False, generic: bool = False, z_slab=None, device: int = 0, fused: bool = False):
+    backend = b200.FdtdB200Backend(device=device, exact_arithmetic=exact, force_generic_kernels=generic, z_slab=z_slab, fused_step=fused)
     inst = backend.create_instance(w.solver_config(), w.domain())
     return inst, inst.create_state()
 
 
-def b200_run(b200, w, n_steps: int, exact: bool = False, generic: bool = False, init=None, probes=None):
-    inst, st = b200_state(b200, w, exact, generic)
+def b200_run(b200, w, n_steps: int, exact: bool = False, generic: bool = False, init=None, probes=None, fused: bool = False):
+    inst, st = b200_state(b200, w, exact, generic, fused=fused)
     if init is not None:
         st.write_field(b200.FieldComponent.E, init[0])
         st.write_field(b200.FieldComponent.H, init[1])
