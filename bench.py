@@ -192,6 +192,10 @@ def run_b200(args) -> None:
     nx, ny, nz = lattice
     z_begin, z_end = partition_z(nz, world)[rank]
     w = build_workload(lattice, z_begin, z_end)
+    if args.pml:
+        if world > 1:
+            raise SystemExit("--pml is a single-GPU measurement")
+        w.pml = fdtd_b200.PmlProfiles.graded(w.solver_config(), args.pml)
     backend = fdtd_b200.FdtdB200Backend(device=local_rank, exact_arithmetic=args.exact, z_slab=(z_begin, z_end) if world > 1 else None,
                                         fused_step=not args.no_fused)
     inst = backend.create_instance(w.solver_config(), w.domain())
@@ -344,7 +348,8 @@ def run_b200(args) -> None:
                                   "Gaussian point source, 8 probes (BASELINE configs[2]; weak-scaled 512^3 cells per GPU for N>1)",
                       "lattice": [nx, ny, nz], "cells_per_gpu": cells_total // n_gpus, "decomposition": f"z-slabs x{n_gpus}",
                       "l2": "working set 25 B/cell x 134M cells per GPU >> 126 MB L2 (no flush needed)",
-                      "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport},
+                      "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport,
+                      **({"cpml_cells_per_face": args.pml, "note": "kernel times include the CPML psi passes of the step"} if args.pml else {})},
            "roofline": roofline, "cpu_baseline": cpu_baseline,
            "e2e": {"value": e2e_value, "unit": "Gcells/s", "h2d_bytes_per_step": 32 * n_src, "d2h_bytes_per_step": 24 * n_pr,
                    "ms_per_step": 1e3 * e2e_s / K},
@@ -365,6 +370,7 @@ def main() -> None:
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--transport", choices=("p2p", "nccl"), default="p2p", help="halo transport for N>1 (p2p needs the fused step)")
     ap.add_argument("--no-fused", action="store_true", help="two-kernel path (in-place, 24 B/cell of field memory) instead of the fused step")
+    ap.add_argument("--pml", type=int, default=0, help="add CPML slabs of this many cells on all six faces (N=1; not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-planes", type=int, default=32, help="z-planes in the CPU legs' sample slab")
     ap.add_argument("--cpu-steps", type=int, default=10)

@@ -499,7 +499,11 @@ int launch_pml_axis(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi
     const dim3 block(32, 8, 1);
     for (int zz = 0; zz < r2; zz += 65535) {  // gridDim.z limit
         const int nzz = std::min(r2 - zz, 65535);
-        const dim3 grid((r0 + 31) / 32, (r1 + 7) / 8, nzz);
+        dim3 grid((r0 + 31) / 32, (r1 + 7) / 8, nzz);
+        if (AXIS == 0) {   // flattened (y, k) plane
+            const int ctas = (r0 * r1 + 255) / 256;
+            grid = dim3(std::min(ctas, 32768), (ctas + 32767) / 32768, nzz);
+        }
         PmlAxisView Q = P;
         int zl = z_lo;
         if (AXIS == 2) Q.k0 = P.k0 + zz; else zl = z_lo + zz;
@@ -552,7 +556,8 @@ template <int EXACT, typename IdxT>
 int launch_e_box(fdtd_b200_handle h, const LatticeView& L, float* const out[3], const CellBox& B) {
     const ForcingView F = forcing_view(h);
     const dim3 block(32, 8, 1);
-    const dim3 grid((B.x1 - B.x0 + 31) / 32, (B.y1 - B.y0 + 7) / 8, std::min(B.z1 - B.z0, 65535));
+    const int ctas = ((B.x1 - B.x0) * (B.y1 - B.y0) + 255) / 256;   // flattened (y, x) rectangle
+    const dim3 grid(std::min(ctas, 32768), (ctas + 32767) / 32768, std::min(B.z1 - B.z0, 65535));
     k_update_e_box<EXACT, IdxT><<<grid, block, 0, h->stream>>>(L, F, out[0], out[1], out[2], B);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());

@@ -35,8 +35,11 @@ k_pml_axis(const LatticeView L, const PmlAxisView P, const float* __restrict__ s
     int x, y, z, k;
     size_t q;  // ψ index
     if (AXIS == 0) {
-        if (r0 >= P.n || r1 >= L.ny) return;
-        k = r0; x = __ldg(P.pos + k); y = r1; z = z_lo + r2;
+        // the slab is only P.n (≈ 2 × thickness) cells wide: threads run over the flattened (y, k) plane so that no lane idles
+        // and the ψ accesses of a warp are contiguous
+        const int t = (blockIdx.y * gridDim.x + blockIdx.x) * (blockDim.x * blockDim.y) + threadIdx.y * blockDim.x + threadIdx.x;
+        if (t >= P.n * L.ny) return;
+        k = t % P.n; y = t / P.n; x = __ldg(P.pos + k); z = z_lo + r2;
         q = (static_cast<size_t>(z) * L.ny + y) * P.n + k;
     } else if (AXIS == 1) {
         if (r0 >= L.nx || r1 >= P.n) return;
@@ -91,9 +94,12 @@ struct CellBox { int x0, x1, y0, y1, z0, z1; };
 template <int EXACT, typename IdxT>
 __global__ void __launch_bounds__(256)
 k_update_e_box(const LatticeView L, const ForcingView F, float* __restrict__ ox, float* __restrict__ oy, float* __restrict__ oz, const CellBox B) {
-    const int x = B.x0 + blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = B.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-    if (x >= B.x1 || y >= B.y1) return;
+    // threads run over the flattened (y, x) rectangle of the box: narrow x ranges (the slabs on the x faces) leave no lane idle
+    const int bw = B.x1 - B.x0;
+    const int t = (blockIdx.y * gridDim.x + blockIdx.x) * (blockDim.x * blockDim.y) + threadIdx.y * blockDim.x + threadIdx.x;
+    if (t >= bw * (B.y1 - B.y0)) return;
+    const int x = B.x0 + t % bw;
+    const int y = B.y0 + t / bw;
     const size_t sy = static_cast<size_t>(L.nx);
     const size_t sz = sy * static_cast<size_t>(L.ny);
     for (int z = B.z0 + blockIdx.z; z < B.z1; z += gridDim.z) {
