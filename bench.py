@@ -188,7 +188,7 @@ def run_b200(args) -> None:
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    lattice = tuple(args.lattice) if args.lattice else lattice_for(n_gpus)
+    lattice = tuple(args.lattice) if args.lattice else ((1024, 1024, 1024) if args.scaling == "strong" else lattice_for(n_gpus))
     nx, ny, nz = lattice
     z_begin, z_end = partition_z(nz, world)[rank]
     w = build_workload(lattice, z_begin, z_end)
@@ -343,11 +343,11 @@ def run_b200(args) -> None:
         cb = time_cpu_reference(lattice, args.cpu_planes, args.cpu_steps, 2)
         cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     out = {"metric": "Yee cell-updates/sec", "value": value, "unit": "Gcells/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
-           "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "ms_per_step": ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": f"heterogeneous {nx}x{ny}x{nz} lattice (64 balls of 4 material kinds) inside the 16-cell graded lossy layer, "
-                                  "Gaussian point source, 8 probes (BASELINE configs[2]; weak-scaled 512^3 cells per GPU for N>1)",
+                                  "Gaussian point source, 8 probes (BASELINE configs[2]; " + ("the same lattice for every N: strong scaling, BASELINE configs[3])" if args.scaling == "strong" else "weak-scaled 512^3 cells per GPU for N>1)"),
                       "lattice": [nx, ny, nz], "cells_per_gpu": cells_total // n_gpus, "decomposition": f"z-slabs x{n_gpus}",
-                      "l2": "working set 25 B/cell x 134M cells per GPU >> 126 MB L2 (no flush needed)",
+                      "l2": f"working set {49 if st.uses_fused else 25} B/cell x {cells_total // n_gpus / 1e6:.0f}M cells per GPU >> 126 MB L2 (no flush needed)",
                       "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport,
                       **({"cpml_cells_per_face": args.pml, "note": "kernel times include the CPML psi passes of the step"} if args.pml else {})},
            "roofline": roofline, "cpu_baseline": cpu_baseline,
@@ -370,6 +370,8 @@ def main() -> None:
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--transport", choices=("p2p", "nccl"), default="p2p", help="halo transport for N>1 (p2p needs the fused step)")
     ap.add_argument("--no-fused", action="store_true", help="two-kernel path (in-place, 24 B/cell of field memory) instead of the fused step")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
+                    help="weak: 512^3 cells per GPU (default, the driver's scaling run); strong: one fixed lattice (1024^3 unless --lattice) for every N")
     ap.add_argument("--pml", type=int, default=0, help="add CPML slabs of this many cells on all six faces (N=1; not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-planes", type=int, default=32, help="z-planes in the CPU legs' sample slab")
