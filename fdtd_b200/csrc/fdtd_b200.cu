@@ -424,7 +424,7 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
 }
 
 template <int EXACT, typename IdxT>
-int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi) {
+int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push) {
     constexpr int BX = 32, BY = 8;
     using LO = FusedLayout<IdxT, BX, BY>;
     if (!h->fused_maps_ready) {
@@ -459,7 +459,14 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi) {
     dim3 block(BX, BY, 1);
     dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0);
-    auto k = k_step_fused<EXACT, IdxT, BX, BY>;
+    auto k = push ? k_step_fused<EXACT, IdxT, BX, BY, true> : k_step_fused<EXACT, IdxT, BX, BY, false>;
+    if (push) {   // boundary planes of the peer-memory transport: results also go into the neighbours' pending-set ghost planes
+        const int pend = h->cur_set ^ 1;
+        if (h->lower.present)
+            for (int c = 0; c < 5; ++c) V.push_down[c] = h->lower.field[pend][c] + h->plane * (h->lower.nzl + 1);
+        if (h->upper.present)
+            for (int c = 0; c < 2; ++c) V.push_up[c] = h->upper.field[pend][c];
+    }
     CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc);
     h->launches += 1;
@@ -664,13 +671,13 @@ void prof_clear(fdtd_b200_handle h) {
 }
 
 // planes [z_lo, z_hi) of the current set → the pending set (no swap)
-int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi) {
+int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi, bool push = false) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
     const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi));
-    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi));
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi, push) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi, push) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi, push));
+    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi, push) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi, push) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi, push));
     if (rc) return rc;
     if (h->has_pml) {
         if (z_lo != 0 || z_hi != static_cast<int>(h->nzl) || h->z_begin != 0 || h->z_end != h->nz)
@@ -1793,8 +1800,12 @@ void p2p_close(fdtd_b200_solver::PeerLink* link) {
 }
 
 // Store this slab's boundary planes of buffer set `set` into the neighbours' ghost planes of the same set, then raise their flags.
-int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st) {
+int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st, bool stored_by_kernel) {
     const size_t plane_bytes = static_cast<size_t>(h->plane) * sizeof(float);
+    if (stored_by_kernel) {   // the boundary CTAs stored the planes themselves (k_step_fused<…, PUSH>); only the one-off index plane is copied
+        if (h->lower.present && !h->p2p_mat_sent)
+            CU_TRY(h, cudaMemcpyAsync(h->lower.mat + h->plane * h->lower.nzl * h->idx_bytes, h->mat, h->plane * h->idx_bytes, cudaMemcpyDeviceToDevice, st));
+    } else {
     if (h->upper.present) {   // my top Ex,Ey → the upper slab's ghost plane below its plane 0
         for (int c = 0; c < 2; ++c)
             CU_TRY(h, cudaMemcpyAsync(h->upper.field[set][c], set_base(h, set, c) + h->plane * h->nzl, plane_bytes, cudaMemcpyDeviceToDevice, st));
@@ -1805,6 +1816,7 @@ int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st) {
                                       cudaMemcpyDeviceToDevice, st));
         if (!h->p2p_mat_sent)
             CU_TRY(h, cudaMemcpyAsync(h->lower.mat + h->plane * h->lower.nzl * h->idx_bytes, h->mat, h->plane * h->idx_bytes, cudaMemcpyDeviceToDevice, st));
+    }
     }
     h->p2p_mat_sent = true;
     h->halo_seq += 1;
@@ -1895,7 +1907,7 @@ int fdtd_b200_p2p_refresh(fdtd_b200_handle h) {
     if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
     if (int rc = set_device(h)) return rc;
     // asynchronous and flag-ordered: the next p2p_step's boundary launch waits on the device for the neighbours' copies
-    return p2p_push(h, h->cur_set, h->stream);
+    return p2p_push(h, h->cur_set, h->stream, false);
 }
 
 int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
@@ -1906,6 +1918,10 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
     const int lo = (split && h->lower.present) ? 1 : 0;
     const int hi = (split && h->upper.present) ? n - 1 : n;
     cudaStream_t S = h->stream, B = h->bstream;
+    // default: the boundary CTAs store into the neighbours' ghost planes themselves; FDTD_B200_P2P_COPY_ENGINE=1 selects
+    // the earlier variant (seven peer cudaMemcpyAsync per step and cut after the boundary kernels) for comparison
+    static const bool copy_engine = [] { const char* e = std::getenv("FDTD_B200_P2P_COPY_ENGINE"); return e && e[0] == '1'; }();
+    const bool in_kernel = !copy_engine;
     // whatever was enqueued on the main stream before (uploads, earlier steps, a refresh) precedes the first boundary launch
     CU_TRY(h, cudaEventRecord(h->ev_main, S));
     for (uint64_t s = 0; s < n_steps; ++s) {
@@ -1914,15 +1930,15 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
         if (int rc = p2p_wait(h, B)) return rc;
         h->stream = B;
         int rc = FDTD_B200_OK;
-        if (!split) rc = launch_fused(h, 0, n);
+        if (!split) rc = launch_fused(h, 0, n, in_kernel);
         else {
-            if (hi < n) rc = launch_fused(h, hi, n);
-            if (!rc && lo > 0) rc = launch_fused(h, 0, lo);
+            if (hi < n) rc = launch_fused(h, hi, n, in_kernel);
+            if (!rc && lo > 0) rc = launch_fused(h, 0, lo, in_kernel);
         }
         h->stream = S;
         if (rc) return rc;
         CU_TRY(h, cudaEventRecord(h->ev_bnd, B));
-        if (int rc2 = p2p_push(h, h->cur_set ^ 1, B)) return rc2;   // the planes just written live in the pending set
+        if (int rc2 = p2p_push(h, h->cur_set ^ 1, B, in_kernel)) return rc2;   // the planes just written live in the pending set
         CU_TRY(h, cudaEventRecord(h->ev_push, B));
         // main stream: interior planes, concurrently with the boundary work above (they read the same current set and write
         // disjoint planes of the pending set); the previous step's boundary planes are ordered by ev_bnd from the last turn

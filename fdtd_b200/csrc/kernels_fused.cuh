@@ -47,6 +47,11 @@ struct FusedView {
     int z_lo, z_hi;       // planes updated by this launch
     int lo_open, hi_open; // a neighbouring slab exists below / above: ghost planes -1 / nz hold its old fields
     float dx[3], inv_dx[3];
+    // PUSH variant (boundary-plane launches of the peer-memory transport): the CTAs that own the slab's first / last plane
+    // also store their results straight into the neighbouring GPUs' ghost planes over NVLink (peer-mapped pointers to the
+    // start of that ghost plane in the neighbour's pending set; null = no neighbour on that side).
+    float* push_down[5];  // E'x E'y E'z H'x H'y of plane 0      → the lower neighbour's ghost plane above its last plane
+    float* push_up[2];    // E'x E'y of plane nz-1               → the upper neighbour's ghost plane below its plane 0
 };
 
 template <typename IdxT, int BX, int BY>
@@ -72,7 +77,7 @@ struct FusedLayout {
     }
 };
 
-template <int EXACT, typename IdxT, int BX, int BY>
+template <int EXACT, typename IdxT, int BX, int BY, bool PUSH = false>
 __global__ void __launch_bounds__(BX * BY, 2)
 k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const ForcingView F, const ProbeView P, const int zc) {
     using LO = FusedLayout<IdxT, BX, BY>;
@@ -246,6 +251,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     if (core && k < n) {                          // this CTA owns H' of its core rows and planes
                         const size_t gi = static_cast<size_t>(zk) * sz + static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
                         st4(V.out[3] + gi, hx); st4(V.out[4] + gi, hy); st4(V.out[5] + gi, hz);
+                        if (PUSH && zk == 0 && V.push_down[3] != nullptr) {
+                            const size_t pi = static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
+                            st4(V.push_down[3] + pi, hx); st4(V.push_down[4] + pi, hy);
+                        }
                     }
                 }
             }
@@ -334,6 +343,11 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             if (core) {
                 const size_t gi = static_cast<size_t>(zp) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
                 st4(V.out[0] + gi, ex); st4(V.out[1] + gi, ey); st4(V.out[2] + gi, ez);
+                if (PUSH) {
+                    const size_t pi = static_cast<size_t>(y) * sy + static_cast<size_t>(x);
+                    if (zp == 0 && V.push_down[0] != nullptr) { st4(V.push_down[0] + pi, ex); st4(V.push_down[1] + pi, ey); st4(V.push_down[2] + pi, ez); }
+                    if (zp == V.nz - 1 && V.push_up[0] != nullptr) { st4(V.push_up[0] + pi, ex); st4(V.push_up[1] + pi, ey); }
+                }
                 if (has_probe) {
                     for (int s = lower_bound_ll(P.cells, P.n, cell); s < P.n; ++s) {
                         const long long c = __ldg(P.cells + s);
