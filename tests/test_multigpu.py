@@ -19,3 +19,13 @@ def test_two_ranks_bit_identical_to_one(b200, overlap, fused, transport):
            "--master-port", "29571", os.path.join(ROOT, "tools", "slab_parity.py"), "128,48,40" if fused == "1" else "64,48,40", "25", overlap, fused, transport]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
+
+
+def test_two_ranks_with_cpml_bit_identical_to_one(b200):
+    """CPML slabs cross the cut (x and y layers) and sit on the outer z faces of both ranks; two-kernel handles over NCCL."""
+    if b200.lib().fdtd_b200_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29572", os.path.join(ROOT, "tools", "slab_parity.py"), "64,48,40", "25", "1", "0", "nccl", "6"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout and "pml=6" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]

@@ -23,6 +23,7 @@ def main():
     overlap = (sys.argv[3] != "0") if len(sys.argv) > 3 else True
     fused = (sys.argv[4] != "0") if len(sys.argv) > 4 else False
     transport = sys.argv[5] if len(sys.argv) > 5 else "nccl"     # nccl | p2p (NVLink peer memory, fused handles only)
+    pml = int(sys.argv[6]) if len(sys.argv) > 6 else 0            # CPML cells per face (two-kernel handles)
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     zb, ze = partition_z(lattice[2], world)[rank]
@@ -33,6 +34,8 @@ def main():
     w.sources = [(src_pt, w.sources[0][1])]
     w.probes = [(lattice[0] // 2 + 3, lattice[1] // 2, cut), (lattice[0] // 2, lattice[1] // 2 + 2, cut - 1), (1, 1, lattice[2] - 1)]
     tab = w.source_table(steps)
+    if pml:
+        w.pml = fdtd_b200.PmlProfiles.graded(w.solver_config(), pml)
     be = fdtd_b200.FdtdB200Backend(device=local, z_slab=(zb, ze), fused_step=fused)
     st = be.create_instance(w.solver_config(), w.domain()).create_state()
     st.register_probes(w.probes)
@@ -59,7 +62,7 @@ def main():
     ok = True
     if rank == 0:
         wf = build_workload(lattice, 0, lattice[2])
-        wf.sources, wf.probes = w.sources, w.probes
+        wf.sources, wf.probes, wf.pml = w.sources, w.probes, w.pml
         full = fdtd_b200.FdtdB200Backend(device=local).create_instance(wf.solver_config(), wf.domain()).create_state()
         full.register_probes(wf.probes)
         full.set_source_table(wf.source_points(), tab)
@@ -68,7 +71,7 @@ def main():
         eg, hg = torch.cat(es).cpu().numpy(), torch.cat(hs).cpu().numpy()
         ok = np.array_equal(eg, ef) and np.array_equal(hg, hf) and np.array_equal(pr.cpu().numpy(), full.read_probes(0, steps))
         ok = ok and bool(np.any(ef)) and st.tick() == steps
-        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} fused={st.uses_fused} transport={transport} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
+        print(f"world={world} lattice={lattice} steps={steps} overlap={overlap} fused={st.uses_fused} transport={transport} pml={pml} exchanges={stepper.exchanges}", "SLAB PARITY OK" if ok else "SLAB PARITY FAILED", flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
