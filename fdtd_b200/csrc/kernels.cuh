@@ -63,6 +63,16 @@ __device__ __forceinline__ float deriv(float hi, float lo, float dx, float inv_d
     return (hi - lo) * inv_dx;
 }
 
+// The same derivative where the Neumann rule is folded into the reciprocal: `inv_masked` is 1/dx, or 0 where the neighbour does
+// not exist (the product is then ±0 instead of a selected +0 — equal as numbers; no contraction, so the non-zero case rounds
+// exactly like deriv<>).  EXACT == 2 divides and needs the select.
+template <int EXACT>
+__device__ __forceinline__ float deriv_masked(float hi, float lo, float dx, float inv_masked, bool in) {
+    if (EXACT == 2) return in ? __fdiv_rn(__fsub_rn(hi, lo), dx) : 0.f;
+    if (EXACT == 1) return __fmul_rn(__fsub_rn(hi, lo), inv_masked);
+    return __fmul_rn(hi - lo, inv_masked);
+}
+
 // a*prev + b*(c - s + psi), psi = 0 (update.wgsl:89,127; cpu/mod.rs:460-461, 502-503).
 template <int EXACT>
 __device__ __forceinline__ float leap(float a, float prev, float b, float c, float s) {

@@ -84,7 +84,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM;
     constexpr int E_COMP = LO::E_COMP, H_COMP = LO::H_COMP;
     static_assert(LO::E_SLOT_BYTES % 128 == 0 && LO::H_SLOT_BYTES % 128 == 0 && LO::HB_BYTES % 128 == 0, "128-byte aligned slots");
-    static_assert(BX % 32 == 0, "warp 0 issues the copies");
+    static_assert(BX == 32 && BY <= 32, "one warp per thread row: the last warp issues the copies and owns the right-column cells");
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers
@@ -203,6 +203,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 Idx4<IdxT>::load(s_mat, static_cast<size_t>(r) * PM + 4 * xq, mk);
                 if (!ok) { mk[0] = mk[1] = mk[2] = mk[3] = 0; }
                 const bool y_in = gy > 0, x_in = gx > 0;
+                const float idy = y_in ? V.inv_dx[1] : 0.f, idz = z_in ? V.inv_dx[2] : 0.f;
                 const long long cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
                 int s0 = 0, cnt = 0;
                 if (has_src) {
@@ -224,10 +225,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const bool xq_in = (q > 0) || x_in;
-                    const float dez_dy = y_in ? deriv<EXACT>(ezv[q], ezym[q], V.dx[1], V.inv_dx[1]) : 0.f;
-                    const float dex_dy = y_in ? deriv<EXACT>(exv[q], exym[q], V.dx[1], V.inv_dx[1]) : 0.f;
-                    const float dey_dz = z_in ? deriv<EXACT>(eyv[q], eyzm[q], V.dx[2], V.inv_dx[2]) : 0.f;
-                    const float dex_dz = z_in ? deriv<EXACT>(exv[q], exzm[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                    const float dez_dy = deriv_masked<EXACT>(ezv[q], ezym[q], V.dx[1], idy, y_in);
+                    const float dex_dy = deriv_masked<EXACT>(exv[q], exym[q], V.dx[1], idy, y_in);
+                    const float dey_dz = deriv_masked<EXACT>(eyv[q], eyzm[q], V.dx[2], idz, z_in);
+                    const float dex_dz = deriv_masked<EXACT>(exv[q], exzm[q], V.dx[2], idz, z_in);
                     const float dez_dx = xq_in ? deriv<EXACT>(ezv[q], ezxm[q], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float dey_dx = xq_in ? deriv<EXACT>(eyv[q], eyxm[q], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float cx = dez_dy - dey_dz;
@@ -259,9 +260,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 }
             }
             // H'y, H'z of the single cell to the right of each row (x1 = x0 + 4*BX): phase B's d/dx of the row's last cell.
-            // Every lane of the row computes the same value (broadcast reads); one lane writes it.
-            if (right) {
-                const int r = ty, cR = 4 + 4 * BX;
+            // The top thread row's warp (no E' work in phase B) computes all BY of them, one row per lane.
+            if (right && producer && lane < BY) {
+                const int r = static_cast<int>(lane), cR = 4 + 4 * BX;
                 const int gy = y0 + r, gx = x0 + 4 * BX;
                 const float* pe = e_cur + (r + 1) * PE + cR;
                 const float ex = pe[0], ex_ym = pe[-PE], ey = pe[E_COMP], ey_l = pe[E_COMP - 1], ez = pe[2 * E_COMP], ez_l = pe[2 * E_COMP - 1];
@@ -285,7 +286,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const float4 c = V.table_in_smem ? s_tab[m1] : __ldg(V.table + m1);
                 const float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
                 const float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
-                if (tx == 0) { hb_w[H_COMP + r * PE + cR] = hy1; hb_w[2 * H_COMP + r * PE + cR] = hz1; }
+                hb_w[H_COMP + r * PE + cR] = hy1; hb_w[2 * H_COMP + r * PE + cR] = hz1;
             }
         }
 
@@ -300,6 +301,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             const float hz_r = ph[2 * H_COMP + 4], hy_r = ph[H_COMP + 4];
             const bool z_in = has_a;                                // H'(z_k) exists inside the lattice
             const bool y_in = y + 1 < V.ny, x_in = x + 4 < V.nx;
+            const float idy = y_in ? V.inv_dx[1] : 0.f, idz = z_in ? V.inv_dx[2] : 0.f;
             const long long cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
             int s0 = 0, cnt = 0;
             if (has_src) {
@@ -321,10 +323,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const bool xq_in = (q < 3) || x_in;
-                const float dhz_dy = y_in ? deriv<EXACT>(hzyp[q], hzv[q], V.dx[1], V.inv_dx[1]) : 0.f;
-                const float dhx_dy = y_in ? deriv<EXACT>(hxyp[q], hxv[q], V.dx[1], V.inv_dx[1]) : 0.f;
-                const float dhy_dz = z_in ? deriv<EXACT>(hyzp[q], hyv[q], V.dx[2], V.inv_dx[2]) : 0.f;
-                const float dhx_dz = z_in ? deriv<EXACT>(hxzp[q], hxv[q], V.dx[2], V.inv_dx[2]) : 0.f;
+                const float dhz_dy = deriv_masked<EXACT>(hzyp[q], hzv[q], V.dx[1], idy, y_in);
+                const float dhx_dy = deriv_masked<EXACT>(hxyp[q], hxv[q], V.dx[1], idy, y_in);
+                const float dhy_dz = deriv_masked<EXACT>(hyzp[q], hyv[q], V.dx[2], idz, z_in);
+                const float dhx_dz = deriv_masked<EXACT>(hxzp[q], hxv[q], V.dx[2], idz, z_in);
                 const float dhz_dx = xq_in ? deriv<EXACT>(hzxp[q], hzv[q], V.dx[0], V.inv_dx[0]) : 0.f;
                 const float dhy_dx = xq_in ? deriv<EXACT>(hyxp[q], hyv[q], V.dx[0], V.inv_dx[0]) : 0.f;
                 const float cx = dhz_dy - dhy_dz;
