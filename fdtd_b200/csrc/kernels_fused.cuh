@@ -87,8 +87,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     static_assert(BX == 32 && BY <= 32, "one warp per thread row: the last warp issues the copies and owns the right-column cells");
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers
-    uint64_t* fullH = fullE + LO::NE;                              // 2 barriers
+    uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers: TMA data of an E ring slot has landed
+    uint64_t* fullH = fullE + LO::NE;                              // 2 barriers: … of an H ring slot
+    uint64_t* emptyE = fullH + LO::NH;                             // 3 barriers: all BY warps have read the slot into registers
+    uint64_t* emptyH = emptyE + LO::NE;                            // 2 barriers
     unsigned char* e_slots = smem_raw + 128;
     unsigned char* h_slots = e_slots + LO::NE * LO::E_SLOT_BYTES;
     float* hb = reinterpret_cast<float*>(h_slots + LO::NH * LO::H_SLOT_BYTES);   // 2 × 3 × H_COMP
@@ -99,6 +101,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     if (tid == 0) {
         for (int s = 0; s < LO::NE; ++s) mbar_init(fullE + s, 1);
         for (int s = 0; s < LO::NH; ++s) mbar_init(fullH + s, 1);
+        for (int s = 0; s < LO::NE; ++s) mbar_init(emptyE + s, BY);
+        for (int s = 0; s < LO::NH; ++s) mbar_init(emptyH + s, BY);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -196,7 +200,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const float4 ex_ym = ld4(pe - PE), ez_ym = ld4(pe + 2 * E_COMP - PE);
                 const float ey_l = pe[E_COMP - 1], ez_l = pe[2 * E_COMP - 1];
                 const float* pl = e_low + (r + 1) * PE + c0;
-                const float4 ex_zm = ld4(pl), ey_zm = ld4(pl + E_COMP);
+                float4 ex_zm = ld4(pl), ey_zm = ld4(pl + E_COMP);
+                if (!z_in) ex_zm = ey_zm = make_float4(0.f, 0.f, 0.f, 0.f);   // no plane below the lattice: that ring slot was never filled, and the masked reciprocal needs finite operands
                 const float* ph = h_old + r * PE + c0;
                 float4 hx = ld4(ph), hy = ld4(ph + H_COMP), hz = ld4(ph + 2 * H_COMP);
                 int mk[4];
@@ -266,7 +271,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const int gy = y0 + r, gx = x0 + 4 * BX;
                 const float* pe = e_cur + (r + 1) * PE + cR;
                 const float ex = pe[0], ex_ym = pe[-PE], ey = pe[E_COMP], ey_l = pe[E_COMP - 1], ez = pe[2 * E_COMP], ez_l = pe[2 * E_COMP - 1];
-                const float ex_zm = e_low[(r + 1) * PE + cR];
+                const float ex_zm = z_in ? e_low[(r + 1) * PE + cR] : 0.f;
                 const float hy = h_old[H_COMP + r * PE + cR], hz = h_old[2 * H_COMP + r * PE + cR];
                 int m1 = static_cast<int>(s_mat[static_cast<size_t>(r) * PM + 4 * BX]);
                 if (gy >= V.ny) m1 = 0;
@@ -288,6 +293,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
                 hb_w[H_COMP + r * PE + cR] = hy1; hb_w[2 * H_COMP + r * PE + cR] = hz1;
             }
+            // this warp holds everything it needs of the old-H slot of z_k in registers: release it to the producer
+            __syncwarp();
+            if (lane == 0) mbar_arrive(emptyH + (k % LO::NH));
         }
 
         // ---- phase B: E'(z_k - 1) on the core tile ----------------------------------------------------------------
@@ -296,6 +304,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (ty + 1) * PE + 4 + 4 * tx;
             const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + 4 * tx;
             float4 ex = ld4(e_own), ey = ld4(e_own + E_COMP), ez = ld4(e_own + 2 * E_COMP);
+            // last read of the old-E slot of plane z_k - 1 by this warp (phase A used it as the plane below)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(emptyE + (k % LO::NE));
             const float4 hz = hzo;
             const float4 hz_yp = ld4(ph + 2 * H_COMP + PE), hx_yp = ld4(ph + PE);
             const float hz_r = ph[2 * H_COMP + 4], hy_r = ph[H_COMP + 4];
@@ -362,12 +373,24 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 }
             }
         }
+        else {
+            // no phase B in this iteration (k == 0, or the top thread row): this warp is done with the E slot of z_k - 1 too
+            __syncwarp();
+            if (lane == 0) mbar_arrive(emptyE + (k % LO::NE));
+        }
+        // Refill as soon as the other warps have drained the slots — the top row's warp has no E' work and waits here in
+        // their stead, so the copies of plane z_k + 2 start about half an iteration before the end-of-iteration barrier.
+        // H ring slot k % 2 held z_k → z_k + 2;  E ring slot k % 3 held plane z_k - 1 → z_k + 2.
+        if (producer && k + 2 < n_h) {
+            if (lane == 0) mbar_wait(emptyH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
+            issue_h(zk + 2, k % LO::NH);
+            if (lane == 0) mbar_wait(emptyE + (k % LO::NE), static_cast<uint32_t>((k / LO::NE) & 1));
+            issue_e(zk + 2, k % LO::NE);
+        }
         hxo = hxn; hyo = hyn; hzo = hzn;
         mk_prev[0] = mk_cur[0]; mk_prev[1] = mk_cur[1]; mk_prev[2] = mk_cur[2]; mk_prev[3] = mk_cur[3];
 
-        __syncthreads();   // H'(z_k) tile complete; old-E plane z_k-1 and the old-H slot of z_k are drained
-        // E ring slot k % 3 held plane z_k - 1 → refill with plane z_k + 2; H ring slot k % 2 held z_k → z_k + 2
-        if (producer && k + 2 < n_h) { issue_e(zk + 2, (k + 3) % LO::NE); issue_h(zk + 2, k % LO::NH); }
+        __syncthreads();   // H'(z_k) tile complete before any warp reads it in the next iteration's phase B
     }
 }
 
