@@ -208,3 +208,21 @@ def test_time_is_accumulated_not_multiplied(oracle):
     for _ in range(7):
         t += 0.1
     assert s.time == t and s.time != 7 * 0.1  # cpu/mod.rs:513
+
+
+def test_config2_full_fixture_is_what_the_oracle_produces(oracle):
+    """tests/golden/config2_full.npz (tools/make_config2_golden.py, 30 min of host time) against a fresh oracle run of the
+    first steps of the same 256³ workload: the fixture the GPU parity test trusts is the oracle's output."""
+    import os
+
+    from fdtd_b200 import configs
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config2_full.npz"))
+    n_steps = 40     # the numerical light cone (one cell per step) reaches the probes 32 cells from the source
+    w = configs.config2_inclusions(256, int(g["steps"]))
+    s = oracle.RefSolver(w.lattice, w.resolution.spatial, w.resolution.temporal, precision=oracle.F32)
+    s.set_materials(w.palette_rows(), w.ids, w.constants.vacuum_permittivity, w.constants.vacuum_permeability)
+    series, _ = s.run(n_steps, w.source_points(), w.source_table(n_steps), [w.cell(p) for p in w.probes])
+    assert np.array_equal(series.astype(np.float32), g["series_f32"][:n_steps])
+    assert g["series_f32"].shape == (5000, 8, 6) and g["series_f64"].shape == (5000, 8, 6)
+    assert np.any(g["series_f32"][:n_steps] != 0)          
