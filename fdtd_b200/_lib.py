@@ -88,6 +88,7 @@ SYMBOLS = {
     "fdtd_b200_pml_coefficients_graded": (C.c_int, [C.c_double, C.POINTER(PhysicalConstants), C.POINTER(GradedPml), C.c_double, _dp, _dp, _dp]),
     "fdtd_b200_set_pml": (C.c_int, [_H, C.c_int, _dp, _dp, _dp, _dp]),
     "fdtd_b200_has_pml": (C.c_int, [_H]),
+    "fdtd_b200_pml_in_kernel": (C.c_int, [_H]),
     "fdtd_b200_pml_state_floats": (C.c_uint64, [_H]),
     "fdtd_b200_read_pml_state": (C.c_int, [_H, _fp]),
     "fdtd_b200_write_pml_state": (C.c_int, [_H, _fp]),

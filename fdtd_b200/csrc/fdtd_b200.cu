@@ -96,9 +96,12 @@ struct fdtd_b200_solver {
         int* d_pos = nullptr;
         float2* d_bc[2] = {nullptr, nullptr};  // [0] H half-step, [1] E half-step
         float* psi[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [half-step][G_ab, G_ac]
+        float* psi_alt[2] = {nullptr, nullptr};  // fused step with the CPML inside the kernel: ψ_H of the pending set
+        int* d_map = nullptr;          // … and coordinate → k (index into pos), -1 outside the slabs
         size_t floats = 0;             // length of each ψ array
     } pml[3];
     bool has_pml = false;
+    bool pml_in_kernel = false;        // the fused kernel's PML instantiation runs the recursion (else: passes over the slabs)
 
     // NVLink peer-memory halo transport (fdtd_b200_p2p_*)
     struct PeerLink {
@@ -424,9 +427,10 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
 }
 
 template <int EXACT, typename IdxT>
-int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push) {
+int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) {
     constexpr int BX = 32, BY = 8;
     using LO = FusedLayout<IdxT, BX, BY>;
+    if (push && pml) return fail(h, FDTD_B200_ESTATE, "the peer-memory boundary launches do not carry a PML");
     if (!h->fused_maps_ready) {
         for (int set = 0; set < 2; ++set) {
             float* const* arr = (set == h->cur_set) ? h->alloc : h->alt_alloc;   // maps start at the lower ghost plane
@@ -456,10 +460,20 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push) {
         zc = 64;
         while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
     }
+    FusedPmlView Q{};
+    if (pml) {
+        zc = std::min(zc, 128);   // FusedPmlSmem::ZMAX planes of per-chunk coefficients
+        for (int a = 0; a < 3; ++a) {
+            const auto& A = h->pml[a];
+            Q.n[a] = A.n; Q.map[a] = A.d_map; Q.bc_h[a] = A.d_bc[0]; Q.bc_e[a] = A.d_bc[1];
+            for (int g = 0; g < 2; ++g) { Q.gh_in[a][g] = A.psi[0][g]; Q.gh_out[a][g] = A.psi_alt[g]; Q.ge[a][g] = A.psi[1][g]; }
+        }
+    }
     dim3 block(BX, BY, 1);
     dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
-    const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0);
-    auto k = push ? k_step_fused<EXACT, IdxT, BX, BY, true> : k_step_fused<EXACT, IdxT, BX, BY, false>;
+    const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0, pml);
+    auto k = pml ? k_step_fused<EXACT, IdxT, BX, BY, false, true>
+                 : (push ? k_step_fused<EXACT, IdxT, BX, BY, true, false> : k_step_fused<EXACT, IdxT, BX, BY, false, false>);
     if (push) {   // boundary planes of the peer-memory transport: results also go into the neighbours' pending-set ghost planes
         const int pend = h->cur_set ^ 1;
         if (h->lower.present)
@@ -468,24 +482,48 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push) {
             for (int c = 0; c < 2; ++c) V.push_up[c] = h->upper.field[pend][c];
     }
     CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc);
+    k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc, Q);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
+    if (pml)   // ψ_H of the pending set becomes current with the fields (the caller commits the step)
+        for (int a = 0; a < 3; ++a)
+            for (int g = 0; g < 2; ++g) std::swap(h->pml[a].psi[0][g], h->pml[a].psi_alt[g]);
     return FDTD_B200_OK;
 }
 
 // ---- CPML passes ---------------------------------------------------------------------------------
+
+// Does the fused kernel's PML instantiation (kernels_fused.cuh) run the recursion, or the passes over the slabs?  In the
+// kernel: fused whole-lattice handles whose x slabs leave the column right of every 128-cell tile free (that recomputed
+// column carries no x-slab ψ) and put at most FusedPmlSmem::XS cells into one tile row.  FDTD_B200_PML_PASSES=1 forces
+// the passes (the two ways agree bit for bit: tests/test_pml_gpu.py).
+void pml_refresh_mode(fdtd_b200_handle h) {
+    h->pml_in_kernel = false;
+    if (!h->has_pml || !h->fused || h->z_begin != 0 || h->z_end != h->nz) return;
+    if (const char* e = std::getenv("FDTD_B200_PML_PASSES")) if (e[0] == '1') return;
+    for (int a = 0; a < 3; ++a)
+        if (h->pml[a].n && (!h->pml[a].d_map || !h->pml[a].psi_alt[0] || !h->pml[a].psi_alt[1])) return;
+    std::vector<int> per_tile(static_cast<size_t>(h->nx / 128 + 1), 0);
+    for (int x : h->pml[0].pos) {
+        if (x > 0 && x % 128 == 0) return;
+        if (++per_tile[static_cast<size_t>(x / 128)] > 32) return;
+    }
+    h->pml_in_kernel = true;
+}
 
 void pml_free_axis(fdtd_b200_handle h, int a) {
     auto& A = h->pml[a];
     if (A.d_pos) cudaFree(A.d_pos);
     for (int k = 0; k < 2; ++k) if (A.d_bc[k]) cudaFree(A.d_bc[k]);
     for (int fld = 0; fld < 2; ++fld) for (int g = 0; g < 2; ++g) if (A.psi[fld][g]) cudaFree(A.psi[fld][g]);
+    for (int g = 0; g < 2; ++g) if (A.psi_alt[g]) cudaFree(A.psi_alt[g]);
+    if (A.d_map) cudaFree(A.d_map);
     A = fdtd_b200_solver::PmlAxis{};
     h->has_pml = h->pml[0].n || h->pml[1].n || h->pml[2].n;
+    pml_refresh_mode(h);
 }
 
-template <int FIELD, int AXIS, typename IdxT>
+template <int FIELD, int AXIS, typename IdxT, int EXACT>
 int launch_pml_axis(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
     const auto& A = h->pml[AXIS];
     if (A.n == 0) return FDTD_B200_OK;
@@ -514,7 +552,7 @@ int launch_pml_axis(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi
         PmlAxisView Q = P;
         int zl = z_lo;
         if (AXIS == 2) Q.k0 = P.k0 + zz; else zl = z_lo + zz;
-        k_pml_axis<FIELD, AXIS, IdxT><<<grid, block, 0, h->stream>>>(L, Q, s0, s1, s2, d0, d1, d2, zl, z_hi);
+        k_pml_axis<FIELD, AXIS, IdxT, EXACT><<<grid, block, 0, h->stream>>>(L, Q, s0, s1, s2, d0, d1, d2, zl, z_hi);
         h->launches += 1;
     }
     CU_TRY(h, cudaGetLastError());
@@ -523,19 +561,24 @@ int launch_pml_axis(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi
 
 // ψ recursion + correction of planes [z_lo, z_hi) after the half-step `FIELD` (0 = H, 1 = E) ran on them.  `L` names the
 // buffers: the E (H) pointers are differentiated, the H (E) pointers corrected.
+template <int FIELD, typename IdxT, int EXACT>
+int launch_pml_axes(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
+    int rc;
+    if ((rc = launch_pml_axis<FIELD, 0, IdxT, EXACT>(h, L, z_lo, z_hi))) return rc;
+    if ((rc = launch_pml_axis<FIELD, 1, IdxT, EXACT>(h, L, z_lo, z_hi))) return rc;
+    return launch_pml_axis<FIELD, 2, IdxT, EXACT>(h, L, z_lo, z_hi);
+}
+
+int arithmetic_mode(fdtd_b200_handle h);
+
 template <int FIELD>
 int launch_pml_on(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
-    int rc;
-    if (h->idx_bytes == 1) {
-        if ((rc = launch_pml_axis<FIELD, 0, uint8_t>(h, L, z_lo, z_hi))) return rc;
-        if ((rc = launch_pml_axis<FIELD, 1, uint8_t>(h, L, z_lo, z_hi))) return rc;
-        if ((rc = launch_pml_axis<FIELD, 2, uint8_t>(h, L, z_lo, z_hi))) return rc;
-    } else {
-        if ((rc = launch_pml_axis<FIELD, 0, uint16_t>(h, L, z_lo, z_hi))) return rc;
-        if ((rc = launch_pml_axis<FIELD, 1, uint16_t>(h, L, z_lo, z_hi))) return rc;
-        if ((rc = launch_pml_axis<FIELD, 2, uint16_t>(h, L, z_lo, z_hi))) return rc;
-    }
-    return FDTD_B200_OK;
+    const int mode = arithmetic_mode(h);
+    if (h->idx_bytes == 1)
+        return mode == 0 ? launch_pml_axes<FIELD, uint8_t, 0>(h, L, z_lo, z_hi)
+                         : (mode == 1 ? launch_pml_axes<FIELD, uint8_t, 1>(h, L, z_lo, z_hi) : launch_pml_axes<FIELD, uint8_t, 2>(h, L, z_lo, z_hi));
+    return mode == 0 ? launch_pml_axes<FIELD, uint16_t, 0>(h, L, z_lo, z_hi)
+                     : (mode == 1 ? launch_pml_axes<FIELD, uint16_t, 1>(h, L, z_lo, z_hi) : launch_pml_axes<FIELD, uint16_t, 2>(h, L, z_lo, z_hi));
 }
 
 int sample_probes(fdtd_b200_handle h, const LatticeView& L, int z_lo, int z_hi) {
@@ -676,14 +719,14 @@ int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi, bool push = false) {
     const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
-    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi, push) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi, push) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi, push));
-    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi, push) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi, push) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi, push));
+    const bool whole = z_lo == 0 && z_hi == static_cast<int>(h->nzl) && h->z_begin == 0 && h->z_end == h->nz;
+    if (h->has_pml && !whole)
+        return fail(h, FDTD_B200_ESTATE, "a fused step with a PML covers whole lattices only; z-slabs use the two-kernel path");
+    const bool pml = h->has_pml && h->pml_in_kernel;
+    if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi, push, pml) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi, push, pml) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi, push, pml));
+    else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi, push, pml) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi, push, pml) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi, push, pml));
     if (rc) return rc;
-    if (h->has_pml) {
-        if (z_lo != 0 || z_hi != static_cast<int>(h->nzl) || h->z_begin != 0 || h->z_end != h->nz)
-            return fail(h, FDTD_B200_ESTATE, "a fused step with a PML covers whole lattices only; z-slabs use the two-kernel path");
-        if ((rc = fused_pml_passes(h))) return rc;
-    }
+    if (h->has_pml && !pml && (rc = fused_pml_passes(h))) return rc;
     return prof_end(h, 0);
 }
 
@@ -1098,15 +1141,28 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
             if ((e = cudaMalloc(&A.psi[fld][g], sizeof(float) * A.floats)) != cudaSuccess) return oom(e);
             if ((e = cudaMemsetAsync(A.psi[fld][g], 0, sizeof(float) * A.floats, h->stream)) != cudaSuccess) return oom(e);
         }
+    std::vector<int> map;
+    if (h->fused) {   // the fused kernel's PML instantiation: ψ_H ping-pong set and the coordinate → k map
+        map.assign(static_cast<size_t>(hi - lo), -1);
+        for (int k = 0; k < A.n; ++k) map[static_cast<size_t>(A.pos[k])] = k;
+        if ((e = cudaMalloc(&A.d_map, sizeof(int) * map.size())) != cudaSuccess) return oom(e);
+        if ((e = cudaMemcpyAsync(A.d_map, map.data(), sizeof(int) * map.size(), cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+        for (int g = 0; g < 2; ++g) {
+            if ((e = cudaMalloc(&A.psi_alt[g], sizeof(float) * A.floats)) != cudaSuccess) return oom(e);
+            if ((e = cudaMemsetAsync(A.psi_alt[g], 0, sizeof(float) * A.floats, h->stream)) != cudaSuccess) return oom(e);
+        }
+    }
     if ((e = cudaMemcpyAsync(A.d_pos, A.pos.data(), sizeof(int) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
     if ((e = cudaMemcpyAsync(A.d_bc[0], bc_h.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
     if ((e = cudaMemcpyAsync(A.d_bc[1], bc_e.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
     if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return oom(e);   // the host vectors go out of scope
     h->has_pml = true;
+    pml_refresh_mode(h);
     return FDTD_B200_OK;
 }
 
 int fdtd_b200_has_pml(fdtd_b200_handle h) { return h && h->has_pml ? 1 : 0; }
+int fdtd_b200_pml_in_kernel(fdtd_b200_handle h) { return h && h->has_pml && h->pml_in_kernel ? 1 : 0; }
 
 uint64_t fdtd_b200_pml_state_floats(fdtd_b200_handle h) {
     if (!h) return 0;

@@ -54,6 +54,43 @@ struct FusedView {
     float* push_up[2];    // E'x E'y of plane nz-1               → the upper neighbour's ghost plane below its plane 0
 };
 
+// CPML inside the fused step (template flag PML; SURVEY §8 f-2, formulas of kernels_pml.cuh).  The ψ recursion of an axis
+// uses the very derivatives the curl needs, so the slabs cost their ψ traffic only.  ψ_H is read by the recomputed halo
+// cells as well, so like the fields it is ping-pong buffered (gh_in → gh_out, written by the owner); ψ_E is touched by the
+// owner of E' alone and advanced in place.  y and z slabs are x-contiguous (one float4 per quad and array); the ψ of the
+// few x-slab cells of a tile row is staged into shared memory by 4-byte cp.async copies issued before the TMA wait.
+struct FusedPmlView {
+    int n[3];                  // PML coordinates per axis (0: none)
+    const int* map[3];         // coordinate → index into the axis' slab list, -1 outside the slabs
+    const float2* bc_h[3];     // (b, c) per slab index, H half-step
+    const float2* bc_e[3];     // … E half-step
+    const float* gh_in[3][2];  // ψ_H of the current set: G_ab, G_ac   layouts: x [z][y][k], y [z][k][x], z [k][y][x]
+    float* gh_out[3][2];       // ψ_H of the pending set
+    float* ge[3][2];           // ψ_E
+};
+
+template <int BY>
+struct FusedPmlSmem {
+    static constexpr int XS = 32;     // x-slab cells of one tile row (both faces of a one-tile lattice: 2 × 16)
+    static constexpr int ZMAX = 132;  // planes of one chunk + the recomputed plane above it
+    float xs[2][2][BY][XS];           // staged ψ of the x slabs: [half-step][G_ab | G_ac][row][entry]
+    float2 xbc[2][XS];                // (b, c) of each entry: [half-step]
+    int xk[XS];                       // slab index of each entry
+    int xl[XS];                       // tile column of each entry
+    signed char xj[128];              // tile column → entry, -1 outside the slabs
+    int wcnt[4];
+    int yk[BY];
+    float2 ybc[2][BY];
+    int zk[ZMAX];
+    float2 zbc[2][ZMAX];
+};
+
+__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 template <typename IdxT, int BX, int BY>
 struct FusedLayout {
     static constexpr int NT = BX * BY;
@@ -71,15 +108,15 @@ struct FusedLayout {
     static constexpr int H_SLOT_BYTES = 3 * H_COMP * 4 + MAT_BYTES;
     static constexpr int HB_BYTES = 3 * H_COMP * 4;
     static constexpr int NE = 3, NH = 2;                        // ring depths
-    static constexpr size_t smem_bytes(int n_table_in_smem) {
+    static constexpr size_t smem_bytes(int n_table_in_smem, bool pml = false) {
         return 128 + static_cast<size_t>(NE) * E_SLOT_BYTES + static_cast<size_t>(NH) * H_SLOT_BYTES + 2 * static_cast<size_t>(HB_BYTES) +
-               static_cast<size_t>(n_table_in_smem) * sizeof(float4);
+               static_cast<size_t>(n_table_in_smem) * sizeof(float4) + (pml ? sizeof(FusedPmlSmem<BY>) : 0);
     }
 };
 
-template <int EXACT, typename IdxT, int BX, int BY, bool PUSH = false>
+template <int EXACT, typename IdxT, int BX, int BY, bool PUSH = false, bool PML = false>
 __global__ void __launch_bounds__(BX * BY, 2)
-k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const ForcingView F, const ProbeView P, const int zc) {
+k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const ForcingView F, const ProbeView P, const int zc, const FusedPmlView Q) {
     using LO = FusedLayout<IdxT, BX, BY>;
     constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM;
     constexpr int E_COMP = LO::E_COMP, H_COMP = LO::H_COMP;
@@ -109,13 +146,52 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     if (V.table_in_smem) {
         for (int t = tid; t < V.n_table; t += NT) s_tab[t] = V.table[t];
     }
-    __syncthreads();
-
     const int x0 = blockIdx.x * (4 * BX);
     const int y0 = blockIdx.y * LO::CORE_ROWS;
     const int za = V.z_lo + blockIdx.z * zc;
     const int zb = min(za + zc, V.z_hi);
     const int n = zb - za;
+    // ---- CPML: which of the tile's columns, rows and planes lie in a slab, and their (b, c) ------------------------
+    using PS = FusedPmlSmem<BY>;
+    PS& S = *reinterpret_cast<PS*>(s_tab + (V.table_in_smem ? V.n_table : 0));
+    int x_rank = 0, x_k = -1;
+    if (PML) {
+        static_assert(!PML || (BY >= 4 && 4 * BX == 128), "the first four warps scan the tile's 128 columns");
+        if (tid < 4 * BX) {
+            const int gx = x0 + tid;
+            if (Q.n[0] && gx < V.nx) x_k = __ldg(Q.map[0] + gx);
+            const unsigned m = __ballot_sync(0xffffffffu, x_k >= 0);
+            x_rank = __popc(m & ((1u << lane) - 1u));
+            if (lane == 0) S.wcnt[tid >> 5] = __popc(m);
+        }
+        if (tid < BY) {
+            const int gy = y0 + tid;
+            const int ky = (Q.n[1] && gy < V.ny) ? __ldg(Q.map[1] + gy) : -1;
+            S.yk[tid] = ky;
+            if (ky >= 0) { S.ybc[0][tid] = __ldg(Q.bc_h[1] + ky); S.ybc[1][tid] = __ldg(Q.bc_e[1] + ky); }
+        }
+        for (int t = tid; t <= n && t < PS::ZMAX; t += NT) {
+            const int z = za + t;
+            const int kz = (Q.n[2] && z < V.nz) ? __ldg(Q.map[2] + z) : -1;
+            S.zk[t] = kz;
+            if (kz >= 0) { S.zbc[0][t] = __ldg(Q.bc_h[2] + kz); S.zbc[1][t] = __ldg(Q.bc_e[2] + kz); }
+        }
+    }
+    __syncthreads();
+    int nxs = 0;          // x-slab cells of a tile row (entries of the staging rows)
+    int xjp = -1;         // entries of the own quad's four cells, one signed byte each
+    if (PML) {
+        nxs = S.wcnt[0] + S.wcnt[1] + S.wcnt[2] + S.wcnt[3];
+        if (tid < 4 * BX) {
+            int off = 0;
+            for (int w = 0; w < (tid >> 5); ++w) off += S.wcnt[w];
+            const int j = x_k >= 0 ? off + x_rank : -1;
+            S.xj[tid] = static_cast<signed char>(j);
+            if (j >= 0 && j < PS::XS) { S.xk[j] = x_k; S.xl[j] = tid; S.xbc[0][j] = __ldg(Q.bc_h[0] + x_k); S.xbc[1][j] = __ldg(Q.bc_e[0] + x_k); }
+        }
+        __syncthreads();
+        xjp = *reinterpret_cast<const int*>(&S.xj[4 * threadIdx.x]);
+    }
     const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
     // forcing may hit the recomputed halo as well: test the extended box
     bool has_src = false, has_probe = false;
@@ -176,6 +252,27 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         const float* e_cur = nullptr;
         float4 hxn = hxo, hyn = hyo, hzn = hzo;
         int mk_cur[4] = {0, 0, 0, 0};
+        if (PML) {
+            // ψ of the row's x-slab cells → shared memory, in flight while this warp waits for the TMA data:
+            // ψ_H of plane z_k for phase A and ψ_E of plane z_k - 1 for phase B (each warp stages and reads its own row)
+            if (nxs) {
+                __syncwarp();
+                if (static_cast<int>(lane) < nxs && y < V.ny) {
+                    const int kx = S.xk[lane];
+                    if (has_a) {
+                        const size_t qi = (static_cast<size_t>(zk) * V.ny + y) * Q.n[0] + kx;
+                        cp_async4(&S.xs[0][0][ty][lane], Q.gh_in[0][0] + qi);
+                        cp_async4(&S.xs[0][1][ty][lane], Q.gh_in[0][1] + qi);
+                    }
+                    if (k >= 1 && ty < LO::CORE_ROWS) {
+                        const size_t qi = (static_cast<size_t>(zk - 1) * V.ny + y) * Q.n[0] + kx;
+                        cp_async4(&S.xs[1][0][ty][lane], Q.ge[0][0] + qi);
+                        cp_async4(&S.xs[1][1][ty][lane], Q.ge[0][1] + qi);
+                    }
+                }
+                cp_async_commit();
+            }
+        }
         if (has_a) {
             const int e_idx = k + 1;
             mbar_wait(fullE + (e_idx % LO::NE), static_cast<uint32_t>((e_idx / LO::NE) & 1));
@@ -215,6 +312,28 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     s0 = lower_bound_ll(F.cells, F.n, cell);
                     while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
                 }
+                // CPML, x slabs: lane j advances ψ_H of the row's j-th x-slab cell (∂Ey/∂x, ∂Ez/∂x from the staged E plane) and
+                // leaves the new values in the staging row for the cell's owner; the row's owner stores them
+                const bool own_h = core && k < n;
+                if (PML && nxs) {
+                    cp_async_wait_all();
+                    if (static_cast<int>(lane) < nxs && gy < V.ny) {
+                        const int xl = S.xl[lane];
+                        const float* pj = e_cur + (r + 1) * PE + 4 + xl;
+                        const bool in = x0 + xl > 0;
+                        const float dey = in ? deriv<EXACT>(pj[E_COMP], pj[E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
+                        const float dez = in ? deriv<EXACT>(pj[2 * E_COMP], pj[2 * E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
+                        const float2 bc = S.xbc[0][lane];
+                        const float g0 = fmaf(bc.x, S.xs[0][0][r][lane], bc.y * dey);
+                        const float g1 = fmaf(bc.x, S.xs[0][1][r][lane], bc.y * dez);
+                        S.xs[0][0][r][lane] = g0; S.xs[0][1][r][lane] = g1;
+                        if (k < n && r < LO::CORE_ROWS) {
+                            const size_t qi = (static_cast<size_t>(zk) * V.ny + gy) * Q.n[0] + S.xk[lane];
+                            Q.gh_out[0][0][qi] = g0; Q.gh_out[0][1][qi] = g1;
+                        }
+                    }
+                    __syncwarp();
+                }
                 const float exv[4] = {ex.x, ex.y, ex.z, ex.w};
                 const float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
                 const float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
@@ -245,6 +364,55 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     hxv[q] = leap<EXACT>(c.z, hxv[q], c.w, -cx, mx);
                     hyv[q] = leap<EXACT>(c.z, hyv[q], c.w, -cy, my);
                     hzv[q] = leap<EXACT>(c.z, hzv[q], c.w, -cz, mz);
+                    if (PML && nxs) {   // x slabs: H_y += d_b·G_xz, H_z −= d_b·G_xy (k_pml_axis<0, 0>)
+                        const int j = ok ? (xjp << (24 - 8 * q)) >> 24 : -1;
+                        if (j >= 0) {
+                            hyv[q] = fmaf(c.w, S.xs[0][1][r][j], hyv[q]);
+                            hzv[q] = fmaf(-c.w, S.xs[0][0][r][j], hzv[q]);
+                        }
+                    }
+                }
+                if (PML) {
+                    // y and z slabs (whole rows / planes: warp- and CTA-uniform): G ← b·G + c·∂E/∂x_a from the staged planes
+                    // again, H_b += d_b·G_ac, H_c −= d_b·G_ab; y before z as the passes run (k_pml_axis<0, 1>, <0, 2>)
+                    const int pky = ok ? S.yk[r] : -1, pkz = ok ? S.zk[k] : -1;
+                    if (pky >= 0) {
+                        const size_t qy = (static_cast<size_t>(zk) * Q.n[1] + pky) * sy + gx;
+                        const float4 a = ld4(Q.gh_in[1][0] + qy), b = ld4(Q.gh_in[1][1] + qy);
+                        const float2 bc = S.ybc[0][r];
+                        float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const float w = V.table_in_smem ? s_tab[mk[q]].w : __ldg(V.table + mk[q]).w;
+                            g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(pe[2 * E_COMP + q], pe[2 * E_COMP - PE + q], V.dx[1], idy, y_in));
+                            g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(pe[q], pe[q - PE], V.dx[1], idy, y_in));
+                            hzv[q] = fmaf(w, g1[q], hzv[q]);
+                            hxv[q] = fmaf(-w, g0[q], hxv[q]);
+                        }
+                        if (own_h) {
+                            st4(Q.gh_out[1][0] + qy, make_float4(g0[0], g0[1], g0[2], g0[3]));
+                            st4(Q.gh_out[1][1] + qy, make_float4(g1[0], g1[1], g1[2], g1[3]));
+                        }
+                    }
+                    if (pkz >= 0) {
+                        const size_t qz = (static_cast<size_t>(pkz) * V.ny + gy) * sy + gx;
+                        const float4 a = ld4(Q.gh_in[2][0] + qz), b = ld4(Q.gh_in[2][1] + qz);
+                        const float2 bc = S.zbc[0][k];
+                        float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const float w = V.table_in_smem ? s_tab[mk[q]].w : __ldg(V.table + mk[q]).w;
+                            const float lo_x = z_in ? pl[q] : 0.f, lo_y = z_in ? pl[E_COMP + q] : 0.f;   // as ex_zm, ey_zm above
+                            g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(pe[q], lo_x, V.dx[2], idz, z_in));
+                            g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(pe[E_COMP + q], lo_y, V.dx[2], idz, z_in));
+                            hxv[q] = fmaf(w, g1[q], hxv[q]);
+                            hyv[q] = fmaf(-w, g0[q], hyv[q]);
+                        }
+                        if (own_h) {
+                            st4(Q.gh_out[2][0] + qz, make_float4(g0[0], g0[1], g0[2], g0[3]));
+                            st4(Q.gh_out[2][1] + qz, make_float4(g1[0], g1[1], g1[2], g1[3]));
+                        }
+                    }
                 }
                 hx = make_float4(hxv[0], hxv[1], hxv[2], hxv[3]);
                 hy = make_float4(hyv[0], hyv[1], hyv[2], hyv[3]);
@@ -289,8 +457,23 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     if (s1 < F.n && __ldg(F.cells + s1) == cell) { my = __ldg(F.vals + 6 * s1 + 4); mz = __ldg(F.vals + 6 * s1 + 5); }
                 }
                 const float4 c = V.table_in_smem ? s_tab[m1] : __ldg(V.table + m1);
-                const float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
-                const float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
+                float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
+                float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
+                if (PML && gy < V.ny) {
+                    // the column right of the tile is never in an x slab (host-side eligibility); H'z takes the y slab's
+                    // G_yx (∂Ex/∂y), H'y the z slab's G_zx (∂Ex/∂z) — recomputed, the owner stores them
+                    const int ky = S.yk[r], kz = S.zk[k];
+                    if (ky >= 0) {
+                        const float2 bc = S.ybc[0][r];
+                        const float g1 = fmaf(bc.x, Q.gh_in[1][1][(static_cast<size_t>(zk) * Q.n[1] + ky) * sy + gx], bc.y * dex_dy);
+                        hz1 = fmaf(c.w, g1, hz1);
+                    }
+                    if (kz >= 0) {
+                        const float2 bc = S.zbc[0][k];
+                        const float g0 = fmaf(bc.x, Q.gh_in[2][0][(static_cast<size_t>(kz) * V.ny + gy) * sy + gx], bc.y * dex_dz);
+                        hy1 = fmaf(-c.w, g0, hy1);
+                    }
+                }
                 hb_w[H_COMP + r * PE + cR] = hy1; hb_w[2 * H_COMP + r * PE + cR] = hz1;
             }
             // this warp holds everything it needs of the old-H slot of z_k in registers: release it to the producer
@@ -331,6 +514,25 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             float exv[4] = {ex.x, ex.y, ex.z, ex.w};
             float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
             float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
+            // CPML, x slabs: lane j advances ψ_E of the row's j-th x-slab cell (∂H'y/∂x, ∂H'z/∂x from the exchanged H' tile of
+            // plane z_k - 1) in place and leaves the new values in the staging row for the cell's owner
+            if (PML && nxs) {
+                cp_async_wait_all();
+                if (static_cast<int>(lane) < nxs && y < V.ny) {
+                    const int xl = S.xl[lane];
+                    const float* pj = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + xl;
+                    const bool in = x0 + xl + 1 < V.nx;
+                    const float dhy = in ? deriv<EXACT>(pj[H_COMP + 1], pj[H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float dhz = in ? deriv<EXACT>(pj[2 * H_COMP + 1], pj[2 * H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float2 bc = S.xbc[1][lane];
+                    const float g0 = fmaf(bc.x, S.xs[1][0][ty][lane], bc.y * dhy);
+                    const float g1 = fmaf(bc.x, S.xs[1][1][ty][lane], bc.y * dhz);
+                    S.xs[1][0][ty][lane] = g0; S.xs[1][1][ty][lane] = g1;
+                    const size_t qi = (static_cast<size_t>(zp) * V.ny + y) * Q.n[0] + S.xk[lane];
+                    Q.ge[0][0][qi] = g0; Q.ge[0][1][qi] = g1;
+                }
+                __syncwarp();
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const bool xq_in = (q < 3) || x_in;
@@ -349,6 +551,49 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 exv[q] = leap<EXACT>(c.x, exv[q], c.y, cx, jx);
                 eyv[q] = leap<EXACT>(c.x, eyv[q], c.y, cy, jy);
                 ezv[q] = leap<EXACT>(c.x, ezv[q], c.y, cz, jz);
+                if (PML && nxs) {   // x slabs: E_y −= c_b·G_xz, E_z += c_b·G_xy (k_pml_axis<1, 0>)
+                    const int j = core ? (xjp << (24 - 8 * q)) >> 24 : -1;
+                    if (j >= 0) {
+                        eyv[q] = fmaf(-c.y, S.xs[1][1][ty][j], eyv[q]);
+                        ezv[q] = fmaf(c.y, S.xs[1][0][ty][j], ezv[q]);
+                    }
+                }
+            }
+            if (PML) {
+                // y and z slabs: ψ_E advanced in place by the owner of E' (k_pml_axis<1, 1>, <1, 2>): E_b −= c_b·G_ac, E_c += c_b·G_ab
+                const int pky = core ? S.yk[ty] : -1, pkz = core ? S.zk[k - 1] : -1;
+                if (pky >= 0) {
+                    const size_t qy = (static_cast<size_t>(zp) * Q.n[1] + pky) * sy + x;
+                    const float4 a = ld4(Q.ge[1][0] + qy), b = ld4(Q.ge[1][1] + qy);
+                    const float2 bc = S.ybc[1][ty];
+                    float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float w = V.table_in_smem ? s_tab[mk_prev[q]].y : __ldg(V.table + mk_prev[q]).y;
+                        g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(hzyp[q], hzv[q], V.dx[1], idy, y_in));
+                        g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(hxyp[q], hxv[q], V.dx[1], idy, y_in));
+                        ezv[q] = fmaf(-w, g1[q], ezv[q]);
+                        exv[q] = fmaf(w, g0[q], exv[q]);
+                    }
+                    st4(Q.ge[1][0] + qy, make_float4(g0[0], g0[1], g0[2], g0[3]));
+                    st4(Q.ge[1][1] + qy, make_float4(g1[0], g1[1], g1[2], g1[3]));
+                }
+                if (pkz >= 0) {
+                    const size_t qz = (static_cast<size_t>(pkz) * V.ny + y) * sy + x;
+                    const float4 a = ld4(Q.ge[2][0] + qz), b = ld4(Q.ge[2][1] + qz);
+                    const float2 bc = S.zbc[1][k - 1];
+                    float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float w = V.table_in_smem ? s_tab[mk_prev[q]].y : __ldg(V.table + mk_prev[q]).y;
+                        g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(hxzp[q], hxv[q], V.dx[2], idz, z_in));
+                        g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(hyzp[q], hyv[q], V.dx[2], idz, z_in));
+                        exv[q] = fmaf(-w, g1[q], exv[q]);
+                        eyv[q] = fmaf(w, g0[q], eyv[q]);
+                    }
+                    st4(Q.ge[2][0] + qz, make_float4(g0[0], g0[1], g0[2], g0[3]));
+                    st4(Q.ge[2][1] + qz, make_float4(g1[0], g1[1], g1[2], g1[3]));
+                }
             }
             ex = make_float4(exv[0], exv[1], exv[2], exv[3]);
             ey = make_float4(eyv[0], eyv[1], eyv[2], eyv[3]);

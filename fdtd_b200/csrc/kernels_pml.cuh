@@ -25,7 +25,8 @@ struct PmlAxisView {
 
 // FIELD 0: H half-step (backward differences of E), 1: E half-step (forward differences of H').
 // `src` are the three components differentiated, `dst` the three components corrected (may belong to different buffer sets).
-template <int FIELD, int AXIS, typename IdxT>
+// EXACT: the arithmetic mode of the half-step kernels (kernels.cuh), so that ψ sees the very derivatives the curl used.
+template <int FIELD, int AXIS, typename IdxT, int EXACT>
 __global__ void __launch_bounds__(256)
 k_pml_axis(const LatticeView L, const PmlAxisView P, const float* __restrict__ s0, const float* __restrict__ s1, const float* __restrict__ s2,
            float* d0, float* d1, float* d2, const int z_lo, const int z_hi) {
@@ -66,10 +67,10 @@ k_pml_axis(const LatticeView L, const PmlAxisView P, const float* __restrict__ s
     float dfb = 0.f, dfc = 0.f;
     if (FIELD == 0) {
         const bool in = coord > 0 || (AXIS == 2 && L.lo_open);
-        if (in) { dfb = (sb[i] - sb[i - stride]) * L.inv_dx[AXIS]; dfc = (sc[i] - sc[i - stride]) * L.inv_dx[AXIS]; }
+        if (in) { dfb = deriv<EXACT>(sb[i], sb[i - stride], L.dx[AXIS], L.inv_dx[AXIS]); dfc = deriv<EXACT>(sc[i], sc[i - stride], L.dx[AXIS], L.inv_dx[AXIS]); }
     } else {
         const bool in = coord + 1 < extent || (AXIS == 2 && L.hi_open);
-        if (in) { dfb = (sb[i + stride] - sb[i]) * L.inv_dx[AXIS]; dfc = (sc[i + stride] - sc[i]) * L.inv_dx[AXIS]; }
+        if (in) { dfb = deriv<EXACT>(sb[i + stride], sb[i], L.dx[AXIS], L.inv_dx[AXIS]); dfc = deriv<EXACT>(sc[i + stride], sc[i], L.dx[AXIS], L.inv_dx[AXIS]); }
     }
     const float2 bc = __ldg(P.bc + k);
     const float g0 = fmaf(bc.x, P.g0[q], bc.y * dfb);

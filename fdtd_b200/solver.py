@@ -456,6 +456,10 @@ class FdtdB200SolverState:
     def has_pml(self) -> bool:
         return bool(self._lib.fdtd_b200_has_pml(self._h))
 
+    def pml_in_kernel(self) -> bool:
+        """True when the fused step kernel advances ψ itself (no separate PML passes)."""
+        return bool(self._lib.fdtd_b200_pml_in_kernel(self._h))
+
     def read_pml_state(self) -> np.ndarray:
         out = np.zeros(int(self._lib.fdtd_b200_pml_state_floats(self._h)), dtype=np.float32)
         L.check(self._lib.fdtd_b200_read_pml_state(self._h, out.ctypes.data_as(C.POINTER(C.c_float))), self._h)

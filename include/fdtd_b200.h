@@ -188,10 +188,13 @@ int fdtd_b200_pml_coefficients(double dt, const fdtd_b200_physical_constants* co
 int fdtd_b200_pml_coefficients_graded(double dt, const fdtd_b200_physical_constants* constants, const fdtd_b200_graded_pml* g, double depth,
                                       const double normal[3], double b_out[3], double c_out[3]);
 /* Profiles of one axis (arrays of the global extent of that axis); b_e == NULL clears the axis.  ψ starts at zero.
- * Fused-step handles run the PML as extra passes after the fused kernel (whole lattices only); z-slab handles must be
- * two-kernel handles; not available with the peer-memory transport. */
+ * Fused-step handles (whole lattices only) run the recursion inside the fused kernel when the x slabs fit its tiling
+ * (no PML coordinate at a multiple of 128 other than 0, at most 32 per 128-cell tile; FDTD_B200_PML_PASSES=1 in the
+ * environment forces the alternative), else as extra passes after it; z-slab handles must be two-kernel handles; not
+ * available with the peer-memory transport. */
 int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const double* c_e, const double* b_h, const double* c_h);
 int fdtd_b200_has_pml(fdtd_b200_handle h);
+int fdtd_b200_pml_in_kernel(fdtd_b200_handle h);   /* 1 when the fused kernel itself advances ψ (no PML passes) */
 /* ψ state for checkpoints: all ψ arrays of this handle, concatenated. */
 uint64_t fdtd_b200_pml_state_floats(fdtd_b200_handle h);
 int fdtd_b200_read_pml_state(fdtd_b200_handle h, float* out);

@@ -226,3 +226,32 @@ def test_config2_full_fixture_is_what_the_oracle_produces(oracle):
     assert np.array_equal(series.astype(np.float32), g["series_f32"][:n_steps])
     assert g["series_f32"].shape == (5000, 8, 6) and g["series_f64"].shape == (5000, 8, 6)
     assert np.any(g["series_f32"][:n_steps] != 0)          
+
+
+def test_config3_full_fixture_is_what_the_oracle_produces(oracle):
+    """tests/golden/config3_full.npz (tools/make_config3_golden.py: the 512³ bench workload, 200 steps) against a fresh oracle
+    run of the same sources on the slab of planes around the source plane, for as many steps as the numerical light cone
+    (one cell per step) needs to reach the slab's faces: inside it the probe series of the slab equal those of the lattice."""
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    from bench import build_workload
+    from fdtd_b200 import configs
+
+    g = np.load(os.path.join(root, "tests", "golden", "config3_full.npz"))
+    assert g["series_f32"].shape == (200, 8, 6) and g["series_f64"].shape == (200, 8, 6) and int(g["steps"]) == 200
+    lattice = tuple(int(v) for v in g["lattice"])
+    half, n_steps = 20, 36     # a disturbance from the slab's faces needs 2 x 20 steps to reach the probe plane
+    z0, z1 = lattice[2] // 2 - half, lattice[2] // 2 + half
+    w = build_workload(lattice, z0, z1)
+    sub = (lattice[0], lattice[1], z1 - z0)
+    s = oracle.RefSolver(sub, w.resolution.spatial, w.resolution.temporal, precision=oracle.F32)
+    s.set_materials(w.palette_rows(), w.ids, w.constants.vacuum_permittivity, w.constants.vacuum_permeability)
+    pts = [(x, y, z - z0) for (x, y, z) in (p for p, _ in w.sources)]
+    cells = [(z - z0) * sub[0] * sub[1] + y * sub[0] + x for (x, y, z) in w.probes]
+    series, _ = s.run(n_steps, pts, w.source_table(n_steps), cells)
+    assert np.array_equal(series.astype(np.float32), g["series_f32"][:n_steps])
+    assert np.any(series[:, 0] != 0) and np.any(series[:, 1] != 0) and np.any(series[:, 4] != 0)   # probes 16 and 32 cells away
+    assert np.array_equal(g["probes"], np.array(w.probes))

@@ -78,6 +78,52 @@ def test_fused_step_with_pml_equals_two_kernel_path(b200, exact):
     assert np.array_equal(a.read_pml_state(), f.read_pml_state())
 
 
+@pytest.mark.parametrize("size,thickness,exact,u16", [
+    ((128, 18, 14), 4, True, False), ((256, 30, 20), 5, True, False), ((256, 30, 20), 9, False, False),
+    ((384, 40, 70), 16, False, False), ((144, 23, 9), 3, True, True),
+])
+def test_pml_inside_the_fused_kernel_equals_the_passes(b200, monkeypatch, size, thickness, exact, u16):
+    """The fused kernel's PML instantiation (ψ_H ping-pong, ψ_E in place, x-slab ψ staged by cp.async) == the fused kernel
+    followed by the slab passes (FDTD_B200_PML_PASSES=1) — bit for bit: fields, probes inside the layers and the ψ state.
+    Lattices with several tiles along x and y, several z chunks, layers that are not quad-aligned, both index widths."""
+    # exact arithmetic with dx = (1, 0.5, 2) is the multiply mode, with dx = (1, 0.3, 2) the IEEE-division mode
+    dx = (1.0, 0.3, 2.0) if (exact and size[0] == 256) else (1.0, 0.5, 2.0)
+    w = _with_pml(b200, _random_workload(b200, size, seed=sum(size), dx=dx, dt=0.1), thickness)
+    if u16:
+        rng = np.random.default_rng(17)
+        w.palette = [b200.Material(relative_permittivity=1.0 + 0.01 * m, eletrical_conductivity=0.001 * m) for m in range(300)]
+        w.ids = rng.integers(0, 300, w.n_cells).astype(np.uint32)
+        w.ids[:300] = np.arange(300)
+    w.sources.append(((1, 2, 1), b200.ContinousWave(0.1, 0.05).with_amplitudes((1.0, 2.0, -1.0), (0.5, 0.0, 0.25))))
+    w.sources.append(((size[0] - 1, size[1] - 2, size[2] - 1), b200.GaussianPulse(1.0, 0.5).with_amplitudes((0.0, 1.0, 0.0), (0.0, 0.0, 2.0))))
+    init = random_fields(w, seed=2)
+    probes = [(0, 0, 0), (2, 3, 1), (size[0] // 2, size[1] // 2, size[2] // 2), (size[0] - 1, size[1] - 1, size[2] - 1), (127, 7, 2)]
+    steps = 7
+    monkeypatch.setenv("FDTD_B200_PML_PASSES", "1")
+    _, p, sp = b200_run(b200, w, steps, exact=exact, init=init, probes=probes, fused=True)
+    monkeypatch.delenv("FDTD_B200_PML_PASSES")
+    _, k, sk = b200_run(b200, w, steps, exact=exact, init=init, probes=probes, fused=True)
+    assert p.uses_fused and k.uses_fused and k.pml_in_kernel() and not p.pml_in_kernel()
+    assert k.index_bytes == (2 if u16 else 1)
+    for comp in (b200.FieldComponent.E, b200.FieldComponent.H):
+        assert np.array_equal(p.read_field(comp), k.read_field(comp))
+    assert np.array_equal(sp, sk)
+    assert np.array_equal(p.read_pml_state(), k.read_pml_state())
+    assert k.kernel_launches < p.kernel_launches
+
+
+def test_pml_layers_the_fused_tiling_cannot_hold_fall_back_to_the_passes(b200):
+    """More than 32 PML columns in one 128-cell tile: the handle runs the slab passes after the fused kernel instead."""
+    size = (128, 12, 10)
+    w = _with_pml(b200, _random_workload(b200, size, seed=9), 20, axes=(0,))
+    init = random_fields(w, seed=3)
+    _, a, _ = b200_run(b200, w, 5, init=init)
+    _, f, _ = b200_run(b200, w, 5, init=init, fused=True)
+    assert f.uses_fused and f.has_pml() and not f.pml_in_kernel()
+    for comp in (b200.FieldComponent.E, b200.FieldComponent.H):
+        assert np.array_equal(a.read_field(comp), f.read_field(comp))
+
+
 def test_pml_on_two_slabs_equals_one_domain(b200):
     from fdtd_b200 import _lib as L
 
