@@ -446,7 +446,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     FusedView V{};
     for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
     V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table);
-    V.table_in_smem = h->n_table <= 64 ? 1 : 0;
+    V.table_in_smem = ((pml && sizeof(IdxT) == 1) || h->n_table <= 64) ? 1 : 0;   // the PML instantiation assumes it for 8-bit indices (≤ 256 rows = 4 KB)
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
     V.z_lo = z_lo; V.z_hi = z_hi;
     V.lo_open = h->z_begin > 0 ? 1 : 0;

@@ -16,6 +16,8 @@
 // Arithmetic = the helpers of kernels.cuh → bit-identical to the two-kernel path.
 #pragma once
 
+#include <type_traits>
+
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched with cudaGetDriverEntryPoint)
 
 #include "kernels_bulk.cuh"
@@ -73,7 +75,7 @@ template <int BY>
 struct FusedPmlSmem {
     static constexpr int XS = 32;     // x-slab cells of one tile row (both faces of a one-tile lattice: 2 × 16)
     static constexpr int ZMAX = 132;  // planes of one chunk + the recomputed plane above it
-    float xs[2][2][BY][XS];           // staged ψ of the x slabs: [half-step][G_ab | G_ac][row][entry]
+    float xs[2][2][2][BY][XS];        // staged ψ of the x slabs: [iteration parity][half-step][G_ab | G_ac][row][entry]
     float2 xbc[2][XS];                // (b, c) of each entry: [half-step]
     int xk[XS];                       // slab index of each entry
     int xl[XS];                       // tile column of each entry
@@ -89,7 +91,7 @@ __device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all_but_last() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
 template <typename IdxT, int BX, int BY>
 struct FusedLayout {
@@ -133,6 +135,15 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     float* hb = reinterpret_cast<float*>(h_slots + LO::NH * LO::H_SLOT_BYTES);   // 2 × 3 × H_COMP
     float4* s_tab = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(hb) + 2 * LO::HB_BYTES);
 
+    // The PML instantiation is bound by instruction issue (≈ 1.5 × the warp instructions of the plain one), so it sheds what it
+    // can: no run-time test of where the coefficient table lives for 8-bit indices (≤ 256 rows are always in shared memory) and
+    // a quad loop without the forcing lookup where the CTA holds no source.  The plain instantiation waits on HBM and measured
+    // 2 % SLOWER with the same trimming (123.9 vs 126.6 Gcells/s at 512³, same box), so it keeps the code it was tuned with.
+    constexpr bool LEAN = PML;
+    auto coef = [&](int m) -> float4 {
+        if (LEAN && sizeof(IdxT) == 1) return s_tab[m];
+        return V.table_in_smem ? s_tab[m] : __ldg(V.table + m);
+    };
     const int tid = threadIdx.y * BX + threadIdx.x;
     const unsigned lane = tid & 31u;
     if (tid == 0) {
@@ -246,32 +257,38 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     float4 hxo = make_float4(0.f, 0.f, 0.f, 0.f), hyo = hxo, hzo = hxo;   // H'(z_k) of the own quad
     int mk_prev[4] = {0, 0, 0, 0};
 
+    // CPML: ψ of the row's x-slab cells for iteration kk → shared memory (4-byte cp.async copies, one entry per lane; each
+    // warp stages and reads its own row): ψ_H of plane z_kk for phase A, ψ_E of plane z_kk - 1 for phase B.  One commit
+    // group per call, also when nothing is copied, so that "all but the last group" is always "everything of this iteration".
+    auto stage_x = [&](int kk) {
+        if (PML) {
+            __syncwarp();
+            if (kk <= n && static_cast<int>(lane) < nxs && y < V.ny) {
+                const int kx = S.xk[lane];
+                if (kk < n_h) {
+                    const size_t qi = (static_cast<size_t>(za + kk) * V.ny + y) * Q.n[0] + kx;
+                    cp_async4(&S.xs[kk & 1][0][0][ty][lane], Q.gh_in[0][0] + qi);
+                    cp_async4(&S.xs[kk & 1][0][1][ty][lane], Q.gh_in[0][1] + qi);
+                }
+                if (kk >= 1 && ty < LO::CORE_ROWS) {
+                    const size_t qi = (static_cast<size_t>(za + kk - 1) * V.ny + y) * Q.n[0] + kx;
+                    cp_async4(&S.xs[kk & 1][1][0][ty][lane], Q.ge[0][0] + qi);
+                    cp_async4(&S.xs[kk & 1][1][1][ty][lane], Q.ge[0][1] + qi);
+                }
+            }
+            cp_async_commit();
+        }
+    };
+
     for (int k = 0; k <= n; ++k) {
         const int zk = za + k;
         const bool has_a = k < n_h;
         const float* e_cur = nullptr;
         float4 hxn = hxo, hyn = hyo, hzn = hzo;
         int mk_cur[4] = {0, 0, 0, 0};
-        if (PML) {
-            // ψ of the row's x-slab cells → shared memory, in flight while this warp waits for the TMA data:
-            // ψ_H of plane z_k for phase A and ψ_E of plane z_k - 1 for phase B (each warp stages and reads its own row)
-            if (nxs) {
-                __syncwarp();
-                if (static_cast<int>(lane) < nxs && y < V.ny) {
-                    const int kx = S.xk[lane];
-                    if (has_a) {
-                        const size_t qi = (static_cast<size_t>(zk) * V.ny + y) * Q.n[0] + kx;
-                        cp_async4(&S.xs[0][0][ty][lane], Q.gh_in[0][0] + qi);
-                        cp_async4(&S.xs[0][1][ty][lane], Q.gh_in[0][1] + qi);
-                    }
-                    if (k >= 1 && ty < LO::CORE_ROWS) {
-                        const size_t qi = (static_cast<size_t>(zk - 1) * V.ny + y) * Q.n[0] + kx;
-                        cp_async4(&S.xs[1][0][ty][lane], Q.ge[0][0] + qi);
-                        cp_async4(&S.xs[1][1][ty][lane], Q.ge[0][1] + qi);
-                    }
-                }
-                cp_async_commit();
-            }
+        if (PML && nxs) {
+            if (k == 0) stage_x(0);
+            stage_x(k + 1);          // one iteration ahead, like the TMA rings: its latency hides behind this iteration's work
         }
         if (has_a) {
             const int e_idx = k + 1;
@@ -306,9 +323,11 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 if (!ok) { mk[0] = mk[1] = mk[2] = mk[3] = 0; }
                 const bool y_in = gy > 0, x_in = gx > 0;
                 const float idy = y_in ? V.inv_dx[1] : 0.f, idz = z_in ? V.inv_dx[2] : 0.f;
-                const long long cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
+                long long cell = 0;
                 int s0 = 0, cnt = 0;
+                if (!LEAN) cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
                 if (has_src) {
+                    if (LEAN) cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
                     s0 = lower_bound_ll(F.cells, F.n, cell);
                     while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
                 }
@@ -316,7 +335,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 // leaves the new values in the staging row for the cell's owner; the row's owner stores them
                 const bool own_h = core && k < n;
                 if (PML && nxs) {
-                    cp_async_wait_all();
+                    cp_async_wait_all_but_last();
                     if (static_cast<int>(lane) < nxs && gy < V.ny) {
                         const int xl = S.xl[lane];
                         const float* pj = e_cur + (r + 1) * PE + 4 + xl;
@@ -324,9 +343,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                         const float dey = in ? deriv<EXACT>(pj[E_COMP], pj[E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
                         const float dez = in ? deriv<EXACT>(pj[2 * E_COMP], pj[2 * E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
                         const float2 bc = S.xbc[0][lane];
-                        const float g0 = fmaf(bc.x, S.xs[0][0][r][lane], bc.y * dey);
-                        const float g1 = fmaf(bc.x, S.xs[0][1][r][lane], bc.y * dez);
-                        S.xs[0][0][r][lane] = g0; S.xs[0][1][r][lane] = g1;
+                        const float g0 = fmaf(bc.x, S.xs[k & 1][0][0][r][lane], bc.y * dey);
+                        const float g1 = fmaf(bc.x, S.xs[k & 1][0][1][r][lane], bc.y * dez);
+                        S.xs[k & 1][0][0][r][lane] = g0; S.xs[k & 1][0][1][r][lane] = g1;
                         if (k < n && r < LO::CORE_ROWS) {
                             const size_t qi = (static_cast<size_t>(zk) * V.ny + gy) * Q.n[0] + S.xk[lane];
                             Q.gh_out[0][0][qi] = g0; Q.gh_out[0][1][qi] = g1;
@@ -346,6 +365,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 float hxv[4] = {hx.x, hx.y, hx.z, hx.w};
                 float hyv[4] = {hy.x, hy.y, hy.z, hy.w};
                 float hzv[4] = {hz.x, hz.y, hz.z, hz.w};
+                // the quad's four cells; instantiated with and without the forcing lookup (one CTA in thousands holds a source)
+                auto h_quad = [&](auto with_src) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const bool xq_in = (q > 0) || x_in;
@@ -359,19 +380,21 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     const float cy = dex_dz - dez_dx;
                     const float cz = dey_dx - dex_dy;
                     float mx = 0.f, my = 0.f, mz = 0.f;
-                    if (cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 3); mx = v.x; my = v.y; mz = v.z; }
-                    const float4 c = V.table_in_smem ? s_tab[mk[q]] : __ldg(V.table + mk[q]);
+                    if (decltype(with_src)::value && cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 3); mx = v.x; my = v.y; mz = v.z; }
+                    const float4 c = coef(mk[q]);
                     hxv[q] = leap<EXACT>(c.z, hxv[q], c.w, -cx, mx);
                     hyv[q] = leap<EXACT>(c.z, hyv[q], c.w, -cy, my);
                     hzv[q] = leap<EXACT>(c.z, hzv[q], c.w, -cz, mz);
                     if (PML && nxs) {   // x slabs: H_y += d_b·G_xz, H_z −= d_b·G_xy (k_pml_axis<0, 0>)
                         const int j = ok ? (xjp << (24 - 8 * q)) >> 24 : -1;
                         if (j >= 0) {
-                            hyv[q] = fmaf(c.w, S.xs[0][1][r][j], hyv[q]);
-                            hzv[q] = fmaf(-c.w, S.xs[0][0][r][j], hzv[q]);
+                            hyv[q] = fmaf(c.w, S.xs[k & 1][0][1][r][j], hyv[q]);
+                            hzv[q] = fmaf(-c.w, S.xs[k & 1][0][0][r][j], hzv[q]);
                         }
                     }
                 }
+                };
+                if (!LEAN || has_src) h_quad(std::true_type{}); else h_quad(std::false_type{});
                 if (PML) {
                     // y and z slabs (whole rows / planes: warp- and CTA-uniform): G ← b·G + c·∂E/∂x_a from the staged planes
                     // again, H_b += d_b·G_ac, H_c −= d_b·G_ab; y before z as the passes run (k_pml_axis<0, 1>, <0, 2>)
@@ -383,7 +406,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                         float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            const float w = V.table_in_smem ? s_tab[mk[q]].w : __ldg(V.table + mk[q]).w;
+                            const float w = coef(mk[q]).w;
                             g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(pe[2 * E_COMP + q], pe[2 * E_COMP - PE + q], V.dx[1], idy, y_in));
                             g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(pe[q], pe[q - PE], V.dx[1], idy, y_in));
                             hzv[q] = fmaf(w, g1[q], hzv[q]);
@@ -401,7 +424,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                         float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            const float w = V.table_in_smem ? s_tab[mk[q]].w : __ldg(V.table + mk[q]).w;
+                            const float w = coef(mk[q]).w;
                             const float lo_x = z_in ? pl[q] : 0.f, lo_y = z_in ? pl[E_COMP + q] : 0.f;   // as ex_zm, ey_zm above
                             g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(pe[q], lo_x, V.dx[2], idz, z_in));
                             g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(pe[E_COMP + q], lo_y, V.dx[2], idz, z_in));
@@ -456,7 +479,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     const int s1 = lower_bound_ll(F.cells, F.n, cell);
                     if (s1 < F.n && __ldg(F.cells + s1) == cell) { my = __ldg(F.vals + 6 * s1 + 4); mz = __ldg(F.vals + 6 * s1 + 5); }
                 }
-                const float4 c = V.table_in_smem ? s_tab[m1] : __ldg(V.table + m1);
+                const float4 c = coef(m1);
                 float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
                 float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
                 if (PML && gy < V.ny) {
@@ -496,9 +519,11 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             const bool z_in = has_a;                                // H'(z_k) exists inside the lattice
             const bool y_in = y + 1 < V.ny, x_in = x + 4 < V.nx;
             const float idy = y_in ? V.inv_dx[1] : 0.f, idz = z_in ? V.inv_dx[2] : 0.f;
-            const long long cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
+            long long cell = 0;
             int s0 = 0, cnt = 0;
+            if (!LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
             if (has_src) {
+                if (LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
                 s0 = lower_bound_ll(F.cells, F.n, cell);
                 while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
             }
@@ -517,7 +542,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             // CPML, x slabs: lane j advances ψ_E of the row's j-th x-slab cell (∂H'y/∂x, ∂H'z/∂x from the exchanged H' tile of
             // plane z_k - 1) in place and leaves the new values in the staging row for the cell's owner
             if (PML && nxs) {
-                cp_async_wait_all();
+                cp_async_wait_all_but_last();
                 if (static_cast<int>(lane) < nxs && y < V.ny) {
                     const int xl = S.xl[lane];
                     const float* pj = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + xl;
@@ -525,14 +550,15 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     const float dhy = in ? deriv<EXACT>(pj[H_COMP + 1], pj[H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float dhz = in ? deriv<EXACT>(pj[2 * H_COMP + 1], pj[2 * H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float2 bc = S.xbc[1][lane];
-                    const float g0 = fmaf(bc.x, S.xs[1][0][ty][lane], bc.y * dhy);
-                    const float g1 = fmaf(bc.x, S.xs[1][1][ty][lane], bc.y * dhz);
-                    S.xs[1][0][ty][lane] = g0; S.xs[1][1][ty][lane] = g1;
+                    const float g0 = fmaf(bc.x, S.xs[k & 1][1][0][ty][lane], bc.y * dhy);
+                    const float g1 = fmaf(bc.x, S.xs[k & 1][1][1][ty][lane], bc.y * dhz);
+                    S.xs[k & 1][1][0][ty][lane] = g0; S.xs[k & 1][1][1][ty][lane] = g1;
                     const size_t qi = (static_cast<size_t>(zp) * V.ny + y) * Q.n[0] + S.xk[lane];
                     Q.ge[0][0][qi] = g0; Q.ge[0][1][qi] = g1;
                 }
                 __syncwarp();
             }
+            auto e_quad = [&](auto with_src) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const bool xq_in = (q < 3) || x_in;
@@ -546,19 +572,21 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const float cy = dhx_dz - dhz_dx;
                 const float cz = dhy_dx - dhx_dy;
                 float jx = 0.f, jy = 0.f, jz = 0.f;
-                if (cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 0); jx = v.x; jy = v.y; jz = v.z; }
-                const float4 c = V.table_in_smem ? s_tab[mk_prev[q]] : __ldg(V.table + mk_prev[q]);
+                if (decltype(with_src)::value && cnt) { const float3 v = forcing_lookup(F, s0, cnt, cell + q, 0); jx = v.x; jy = v.y; jz = v.z; }
+                const float4 c = coef(mk_prev[q]);
                 exv[q] = leap<EXACT>(c.x, exv[q], c.y, cx, jx);
                 eyv[q] = leap<EXACT>(c.x, eyv[q], c.y, cy, jy);
                 ezv[q] = leap<EXACT>(c.x, ezv[q], c.y, cz, jz);
                 if (PML && nxs) {   // x slabs: E_y −= c_b·G_xz, E_z += c_b·G_xy (k_pml_axis<1, 0>)
                     const int j = core ? (xjp << (24 - 8 * q)) >> 24 : -1;
                     if (j >= 0) {
-                        eyv[q] = fmaf(-c.y, S.xs[1][1][ty][j], eyv[q]);
-                        ezv[q] = fmaf(c.y, S.xs[1][0][ty][j], ezv[q]);
+                        eyv[q] = fmaf(-c.y, S.xs[k & 1][1][1][ty][j], eyv[q]);
+                        ezv[q] = fmaf(c.y, S.xs[k & 1][1][0][ty][j], ezv[q]);
                     }
                 }
             }
+            };
+            if (!LEAN || has_src) e_quad(std::true_type{}); else e_quad(std::false_type{});
             if (PML) {
                 // y and z slabs: ψ_E advanced in place by the owner of E' (k_pml_axis<1, 1>, <1, 2>): E_b −= c_b·G_ac, E_c += c_b·G_ab
                 const int pky = core ? S.yk[ty] : -1, pkz = core ? S.zk[k - 1] : -1;
@@ -569,7 +597,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const float w = V.table_in_smem ? s_tab[mk_prev[q]].y : __ldg(V.table + mk_prev[q]).y;
+                        const float w = coef(mk_prev[q]).y;
                         g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(hzyp[q], hzv[q], V.dx[1], idy, y_in));
                         g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(hxyp[q], hxv[q], V.dx[1], idy, y_in));
                         ezv[q] = fmaf(-w, g1[q], ezv[q]);
@@ -585,7 +613,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const float w = V.table_in_smem ? s_tab[mk_prev[q]].y : __ldg(V.table + mk_prev[q]).y;
+                        const float w = coef(mk_prev[q]).y;
                         g0[q] = fmaf(bc.x, g0[q], bc.y * deriv_masked<EXACT>(hxzp[q], hxv[q], V.dx[2], idz, z_in));
                         g1[q] = fmaf(bc.x, g1[q], bc.y * deriv_masked<EXACT>(hyzp[q], hyv[q], V.dx[2], idz, z_in));
                         exv[q] = fmaf(-w, g1[q], exv[q]);
@@ -607,6 +635,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     if (zp == V.nz - 1 && V.push_up[0] != nullptr) { st4(V.push_up[0] + pi, ex); st4(V.push_up[1] + pi, ey); }
                 }
                 if (has_probe) {
+                    if (LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
                     for (int s = lower_bound_ll(P.cells, P.n, cell); s < P.n; ++s) {
                         const long long c = __ldg(P.cells + s);
                         if (c >= cell + 4) break;
