@@ -90,6 +90,7 @@ struct FusedPmlSmem {
 __device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all_but_last() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
@@ -289,6 +290,25 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         if (PML && nxs) {
             if (k == 0) stage_x(0);
             stage_x(k + 1);          // one iteration ahead, like the TMA rings: its latency hides behind this iteration's work
+        }
+        if (PML && act) {
+            // the y- and z-slab ψ of the next iteration's quads (plain float4 loads there): pull the lines into L2 now
+            const int kk = k + 1, pky = S.yk[ty];
+            const bool nh = kk < n_h, ne = ty < LO::CORE_ROWS && kk <= n;
+            if (pky >= 0) {
+                const size_t q0 = (static_cast<size_t>(za + kk - 1) * Q.n[1] + pky) * sy + x, dq = static_cast<size_t>(Q.n[1]) * sy;
+                if (nh) { prefetch_l2(Q.gh_in[1][0] + q0 + dq); prefetch_l2(Q.gh_in[1][1] + q0 + dq); }
+                if (ne) { prefetch_l2(Q.ge[1][0] + q0); prefetch_l2(Q.ge[1][1] + q0); }
+            }
+            const int kzh = nh ? S.zk[kk] : -1, kze = ne ? S.zk[kk - 1] : -1;
+            if (kzh >= 0) {
+                const size_t q0 = (static_cast<size_t>(kzh) * V.ny + y) * sy + x;
+                prefetch_l2(Q.gh_in[2][0] + q0); prefetch_l2(Q.gh_in[2][1] + q0);
+            }
+            if (kze >= 0) {
+                const size_t q0 = (static_cast<size_t>(kze) * V.ny + y) * sy + x;
+                prefetch_l2(Q.ge[2][0] + q0); prefetch_l2(Q.ge[2][1] + q0);
+            }
         }
         if (has_a) {
             const int e_idx = k + 1;
