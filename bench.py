@@ -193,8 +193,8 @@ def run_b200(args) -> None:
     z_begin, z_end = partition_z(nz, world)[rank]
     w = build_workload(lattice, z_begin, z_end)
     if args.pml:
-        if world > 1:
-            raise SystemExit("--pml is a single-GPU measurement")
+        if world > 1 and (args.no_fused or args.transport != "p2p"):
+            raise SystemExit("--pml on several GPUs runs inside the fused kernel over the peer-memory transport (drop --no-fused / --transport nccl)")
         w.pml = fdtd_b200.PmlProfiles.graded(w.solver_config(), args.pml)
     backend = fdtd_b200.FdtdB200Backend(device=local_rank, exact_arithmetic=args.exact, z_slab=(z_begin, z_end) if world > 1 else None,
                                         fused_step=not args.no_fused)
@@ -222,6 +222,8 @@ def run_b200(args) -> None:
             else:
                 transport = "p2p (CUDA IPC peer stores + device flags)"
         if stepper is None:
+            if args.pml:
+                raise SystemExit("--pml on several GPUs needs the peer-memory transport, which this box refused")
             engine = CudaSlabEngine(st)
             stepper = SlabStepper(engine, rank, world, overlap=not args.no_overlap)
             transport = "nccl send/recv"
@@ -376,7 +378,7 @@ def main() -> None:
     ap.add_argument("--no-fused", action="store_true", help="two-kernel path (in-place, 24 B/cell of field memory) instead of the fused step")
     ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
                     help="weak: 512^3 cells per GPU (default, the driver's scaling run); strong: one fixed lattice (1024^3 unless --lattice) for every N")
-    ap.add_argument("--pml", type=int, default=0, help="add CPML slabs of this many cells on all six faces (N=1; not the headline workload)")
+    ap.add_argument("--pml", type=int, default=0, help="add CPML slabs of this many cells on all six faces (not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-planes", type=int, default=32, help="z-planes in the CPU legs' sample slab")
     ap.add_argument("--cpu-steps", type=int, default=10)

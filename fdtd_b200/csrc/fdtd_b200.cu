@@ -98,8 +98,14 @@ struct fdtd_b200_solver {
         float* psi[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [half-step][G_ab, G_ac]
         float* psi_alt[2] = {nullptr, nullptr};  // fused step with the CPML inside the kernel: ψ_H of the pending set
         int* d_map = nullptr;          // … and coordinate → k (index into pos), -1 outside the slabs
+        bool ghost = false;            // axis z of a slab: the neighbour's plane above (local coordinate nzl) is a PML coordinate;
+                                       // its (b, c) are entry n of d_bc, its map entry is n
         size_t floats = 0;             // length of each ψ array
     } pml[3];
+    // fused PML on z-slabs: ψ_H of the upper neighbour's first plane, pushed here by that neighbour (peer-memory transport);
+    // two slots by tick parity, each [axis x: G_ab, G_ac | axis y | axis z], plane sizes in ghost_plane[]
+    float* psi_ghost = nullptr;
+    size_t ghost_plane[3] = {0, 0, 0};
     bool has_pml = false;
     bool pml_in_kernel = false;        // the fused kernel's PML instantiation runs the recursion (else: passes over the slabs)
 
@@ -111,6 +117,7 @@ struct fdtd_b200_solver {
         unsigned char* mat = nullptr;
         unsigned long long* flags = nullptr;  // the neighbour's flag words
         std::vector<void*> opened;          // cudaIpcOpenMemHandle results to close
+        float* psi_ghost = nullptr;         // the neighbour's ψ_H receive buffer (lower neighbour only)
     } lower, upper;
     unsigned long long* d_flags = nullptr;  // [0] pushes received from below, [1] from above, [2] flag-wait timeout marker
     uint64_t halo_seq = 0;                  // pushes made to (and expected from) each neighbour so far
@@ -468,6 +475,20 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
             Q.n[a] = A.n; Q.map[a] = A.d_map; Q.bc_h[a] = A.d_bc[0]; Q.bc_e[a] = A.d_bc[1];
             for (int g = 0; g < 2; ++g) { Q.gh_in[a][g] = A.psi[0][g]; Q.gh_out[a][g] = A.psi_alt[g]; Q.ge[a][g] = A.psi[1][g]; }
         }
+        if (V.hi_open) {
+            // the plane above the slab belongs to the upper neighbour: its ψ_H of this step sits in the slot of this tick's parity
+            if (!h->psi_ghost) return fail(h, FDTD_B200_ESTATE, "a fused z-slab with a PML and a neighbour above needs the peer-memory transport (fdtd_b200_p2p_*) for that neighbour's psi");
+            const size_t slot = 2 * (h->ghost_plane[0] + h->ghost_plane[1] + h->ghost_plane[2]);
+            const float* base = h->psi_ghost + (h->tick & 1) * slot;
+            const size_t bias[3] = {static_cast<size_t>(h->nzl) * h->ny * static_cast<size_t>(h->pml[0].n),      // x: [z][y][k] at z = nzl
+                                    static_cast<size_t>(h->nzl) * static_cast<size_t>(h->pml[1].n) * h->nx,      // y: [z][k][x]
+                                    static_cast<size_t>(h->pml[2].n) * h->ny * h->nx};                           // z: [k][y][x] at k = n
+            size_t off = 0;
+            for (int a = 0; a < 3; ++a) {
+                for (int g = 0; g < 2; ++g) Q.gh_ghost[a][g] = base + off + g * h->ghost_plane[a] - bias[a];
+                off += 2 * h->ghost_plane[a];
+            }
+        }
     }
     dim3 block(BX, BY, 1);
     dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
@@ -485,9 +506,6 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc, Q);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
-    if (pml)   // ψ_H of the pending set becomes current with the fields (the caller commits the step)
-        for (int a = 0; a < 3; ++a)
-            for (int g = 0; g < 2; ++g) std::swap(h->pml[a].psi[0][g], h->pml[a].psi_alt[g]);
     return FDTD_B200_OK;
 }
 
@@ -499,10 +517,12 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
 // the passes (the two ways agree bit for bit: tests/test_pml_gpu.py).
 void pml_refresh_mode(fdtd_b200_handle h) {
     h->pml_in_kernel = false;
-    if (!h->has_pml || !h->fused || h->z_begin != 0 || h->z_end != h->nz) return;
+    if (!h->has_pml || !h->fused) return;
     if (const char* e = std::getenv("FDTD_B200_PML_PASSES")) if (e[0] == '1') return;
-    for (int a = 0; a < 3; ++a)
+    for (int a = 0; a < 3; ++a) {
         if (h->pml[a].n && (!h->pml[a].d_map || !h->pml[a].psi_alt[0] || !h->pml[a].psi_alt[1])) return;
+        if (h->pml[a].ghost && !h->pml[a].d_map) return;
+    }
     std::vector<int> per_tile(static_cast<size_t>(h->nx / 128 + 1), 0);
     for (int x : h->pml[0].pos) {
         if (x > 0 && x % 128 == 0) return;
@@ -519,7 +539,7 @@ void pml_free_axis(fdtd_b200_handle h, int a) {
     for (int g = 0; g < 2; ++g) if (A.psi_alt[g]) cudaFree(A.psi_alt[g]);
     if (A.d_map) cudaFree(A.d_map);
     A = fdtd_b200_solver::PmlAxis{};
-    h->has_pml = h->pml[0].n || h->pml[1].n || h->pml[2].n;
+    h->has_pml = h->pml[0].n || h->pml[1].n || h->pml[2].n || h->pml[2].ghost;
     pml_refresh_mode(h);
 }
 
@@ -720,9 +740,9 @@ int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi, bool push = false) {
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
     const bool whole = z_lo == 0 && z_hi == static_cast<int>(h->nzl) && h->z_begin == 0 && h->z_end == h->nz;
-    if (h->has_pml && !whole)
-        return fail(h, FDTD_B200_ESTATE, "a fused step with a PML covers whole lattices only; z-slabs use the two-kernel path");
     const bool pml = h->has_pml && h->pml_in_kernel;
+    if (h->has_pml && !pml && !whole)
+        return fail(h, FDTD_B200_ESTATE, "the PML passes after a fused step cover whole lattices only (plane ranges and z-slabs need the in-kernel PML, see fdtd_b200_pml_in_kernel)");
     if (h->idx_bytes == 1) rc = mode == 0 ? launch_fused_t<0, uint8_t>(h, z_lo, z_hi, push, pml) : (mode == 1 ? launch_fused_t<1, uint8_t>(h, z_lo, z_hi, push, pml) : launch_fused_t<2, uint8_t>(h, z_lo, z_hi, push, pml));
     else rc = mode == 0 ? launch_fused_t<0, uint16_t>(h, z_lo, z_hi, push, pml) : (mode == 1 ? launch_fused_t<1, uint16_t>(h, z_lo, z_hi, push, pml) : launch_fused_t<2, uint16_t>(h, z_lo, z_hi, push, pml));
     if (rc) return rc;
@@ -734,6 +754,9 @@ int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi, bool push = false) {
 void commit_fused(fdtd_b200_handle h) {
     for (int c = 0; c < 6; ++c) { std::swap(h->f[c], h->g[c]); std::swap(h->alloc[c], h->alt_alloc[c]); }
     h->cur_set ^= 1;
+    if (h->has_pml && h->pml_in_kernel)   // ψ_H written by the kernel's PML instantiation becomes current with the fields
+        for (int a = 0; a < 3; ++a)
+            for (int g = 0; g < 2; ++g) std::swap(h->pml[a].psi[0][g], h->pml[a].psi_alt[g]);
 }
 
 void end_step(fdtd_b200_handle h) {
@@ -1004,6 +1027,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
     if (h->d_stage) cudaFree(h->d_stage);
     for (int a = 0; a < 3; ++a) pml_free_axis(h, a);
+    if (h->psi_ghost) cudaFree(h->psi_ghost);
     if (h->bstream) cudaStreamSynchronize(h->bstream);
     for (auto* link : {&h->lower, &h->upper}) { for (void* p : link->opened) cudaIpcCloseMemHandle(p); link->opened.clear(); }
     if (h->d_flags) cudaFree(h->d_flags);
@@ -1105,9 +1129,7 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
     if (axis < 0 || axis > 2) return fail(h, FDTD_B200_EINVAL, "axis must be 0, 1 or 2");
     if ((b_e == nullptr) != (c_e == nullptr) || (b_h == nullptr) != (c_h == nullptr) || (!b_e && b_h))
         return fail(h, FDTD_B200_EINVAL, "pass b and c together (b_h/c_h optional, NULL = the E profile)");
-    if (h->p2p) return fail(h, FDTD_B200_ESTATE, "set the PML before connecting the peer-memory transport (which does not support it)");
-    if (h->fused && (h->z_begin != 0 || h->z_end != h->nz))
-        return fail(h, FDTD_B200_ESTATE, "a PML on z-slabs needs two-kernel handles (create them without FDTD_B200_FUSED_STEP)");
+    if (h->p2p) return fail(h, FDTD_B200_ESTATE, "set the PML before fdtd_b200_p2p_export / connect: the neighbours exchange its layout there");
     if (int rc = set_device(h)) return rc;
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     pml_free_axis(h, axis);
@@ -1127,37 +1149,51 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
         bc_e.push_back(make_float2(static_cast<float>(b_e[i]), static_cast<float>(c_e[i])));
     }
     A.n = static_cast<int>(A.pos.size());
-    if (A.n == 0) { A = fdtd_b200_solver::PmlAxis{}; return FDTD_B200_OK; }
+    // fused z-slabs recompute H' of the neighbour's plane above them: if that plane is a PML coordinate its (b, c) ride along
+    // as entry n (its ψ_H arrives through the peer-memory transport)
+    const bool above = axis == 2 && h->fused && hi < ext;
+    A.ghost = above && (c_e[hi] != 0.0 || c_h[hi] != 0.0);
+    if (A.ghost) {
+        bc_h.push_back(make_float2(static_cast<float>(b_h[hi]), static_cast<float>(c_h[hi])));
+        bc_e.push_back(make_float2(static_cast<float>(b_e[hi]), static_cast<float>(c_e[hi])));
+    }
+    if (A.n == 0 && !A.ghost) { A = fdtd_b200_solver::PmlAxis{}; return FDTD_B200_OK; }
     A.floats = static_cast<size_t>(A.n) * (axis == 0 ? h->ny * h->nzl : (axis == 1 ? h->nx * h->nzl : h->nx * h->ny));
     auto oom = [&](cudaError_t e) {
         pml_free_axis(h, axis);
         return fail(h, e == cudaErrorMemoryAllocation ? FDTD_B200_ENOMEM : FDTD_B200_ECUDA, std::string("PML allocation: ") + cudaGetErrorString(e));
     };
     cudaError_t e;
-    if ((e = cudaMalloc(&A.d_pos, sizeof(int) * A.n)) != cudaSuccess) return oom(e);
-    for (int k = 0; k < 2; ++k) if ((e = cudaMalloc(&A.d_bc[k], sizeof(float2) * A.n)) != cudaSuccess) return oom(e);
-    for (int fld = 0; fld < 2; ++fld)
+    if (A.n && (e = cudaMalloc(&A.d_pos, sizeof(int) * A.n)) != cudaSuccess) return oom(e);
+    for (int k = 0; k < 2; ++k) if ((e = cudaMalloc(&A.d_bc[k], sizeof(float2) * bc_h.size())) != cudaSuccess) return oom(e);
+    for (int fld = 0; fld < 2 && A.n; ++fld)
         for (int g = 0; g < 2; ++g) {
             if ((e = cudaMalloc(&A.psi[fld][g], sizeof(float) * A.floats)) != cudaSuccess) return oom(e);
             if ((e = cudaMemsetAsync(A.psi[fld][g], 0, sizeof(float) * A.floats, h->stream)) != cudaSuccess) return oom(e);
         }
     std::vector<int> map;
-    if (h->fused) {   // the fused kernel's PML instantiation: ψ_H ping-pong set and the coordinate → k map
-        map.assign(static_cast<size_t>(hi - lo), -1);
+    if (h->fused) {   // the fused kernel's PML instantiation: ψ_H ping-pong set and the coordinate → k map (+ the plane above a slab)
+        map.assign(static_cast<size_t>(hi - lo) + (above ? 1 : 0), -1);
         for (int k = 0; k < A.n; ++k) map[static_cast<size_t>(A.pos[k])] = k;
+        if (A.ghost) map[static_cast<size_t>(hi - lo)] = A.n;
         if ((e = cudaMalloc(&A.d_map, sizeof(int) * map.size())) != cudaSuccess) return oom(e);
         if ((e = cudaMemcpyAsync(A.d_map, map.data(), sizeof(int) * map.size(), cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
-        for (int g = 0; g < 2; ++g) {
+        for (int g = 0; g < 2 && A.n; ++g) {
             if ((e = cudaMalloc(&A.psi_alt[g], sizeof(float) * A.floats)) != cudaSuccess) return oom(e);
             if ((e = cudaMemsetAsync(A.psi_alt[g], 0, sizeof(float) * A.floats, h->stream)) != cudaSuccess) return oom(e);
         }
     }
-    if ((e = cudaMemcpyAsync(A.d_pos, A.pos.data(), sizeof(int) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
-    if ((e = cudaMemcpyAsync(A.d_bc[0], bc_h.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
-    if ((e = cudaMemcpyAsync(A.d_bc[1], bc_e.data(), sizeof(float2) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if (A.n && (e = cudaMemcpyAsync(A.d_pos, A.pos.data(), sizeof(int) * A.n, cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if ((e = cudaMemcpyAsync(A.d_bc[0], bc_h.data(), sizeof(float2) * bc_h.size(), cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
+    if ((e = cudaMemcpyAsync(A.d_bc[1], bc_e.data(), sizeof(float2) * bc_e.size(), cudaMemcpyHostToDevice, h->stream)) != cudaSuccess) return oom(e);
     if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return oom(e);   // the host vectors go out of scope
     h->has_pml = true;
     pml_refresh_mode(h);
+    if (h->fused && !h->pml_in_kernel && (h->z_begin != 0 || h->z_end != h->nz)) {
+        pml_free_axis(h, axis);
+        return fail(h, FDTD_B200_ESTATE, "on a fused z-slab the PML must fit the fused kernel's tiling (no PML x-coordinate at a multiple of 128 other "
+                                         "than 0, at most 32 per 128-cell tile, FDTD_B200_PML_PASSES unset); use two-kernel handles otherwise");
+    }
     return FDTD_B200_OK;
 }
 
@@ -1791,6 +1827,11 @@ struct P2PBlob {
     uint64_t nx, ny, nz, z_begin, z_end;
     cudaIpcMemHandle_t field[2][6], mat, flags;
     uint64_t raw_field[2][6], raw_mat, raw_flags;
+    // fused PML on z-slabs: this slab's receive buffer for ψ_H of the plane above it, and the layout both sides must agree on
+    cudaIpcMemHandle_t psi_ghost;
+    uint64_t raw_psi_ghost;
+    uint64_t ghost_plane[3];      // floats per ψ array of that plane, axis x, y, z (0: no PML there / no neighbour above)
+    uint64_t first_plane[3];      // … of THIS slab's first plane: what it will push down
 };
 static_assert(sizeof(P2PBlob) <= FDTD_B200_P2P_BLOB_BYTES, "blob must fit the size the header promises");
 constexpr uint32_t P2P_MAGIC = 0xFD7DB200u;
@@ -1829,6 +1870,7 @@ int p2p_open(fdtd_b200_handle h, const P2PBlob& b, fdtd_b200_solver::PeerLink* l
             for (int c = 0; c < 6; ++c) link->field[s][c] = reinterpret_cast<float*>(b.raw_field[s][c]);
         link->mat = reinterpret_cast<unsigned char*>(b.raw_mat);
         link->flags = reinterpret_cast<unsigned long long*>(b.raw_flags);
+        link->psi_ghost = reinterpret_cast<float*>(b.raw_psi_ghost);
         return FDTD_B200_OK;
     }
     auto open = [&](const cudaIpcMemHandle_t& m, void** out) -> int {
@@ -1846,7 +1888,18 @@ int p2p_open(fdtd_b200_handle h, const P2PBlob& b, fdtd_b200_solver::PeerLink* l
     link->mat = static_cast<unsigned char*>(p);
     if (int rc = open(b.flags, &p)) return rc;
     link->flags = static_cast<unsigned long long*>(p);
+    if (b.raw_psi_ghost) {
+        if (int rc = open(b.psi_ghost, &p)) return rc;
+        link->psi_ghost = static_cast<float*>(p);
+    }
     return FDTD_B200_OK;
+}
+
+// floats per ψ_H array of this slab's first plane, per axis (what the slab below needs of it): x [y][k], y [k][x], z [y][x]
+void pml_first_plane(fdtd_b200_handle h, uint64_t out[3]) {
+    out[0] = static_cast<uint64_t>(h->pml[0].n) * h->ny;
+    out[1] = static_cast<uint64_t>(h->pml[1].n) * h->nx;
+    out[2] = (h->pml[2].n && h->pml[2].pos[0] == 0) ? h->nx * h->ny : 0;
 }
 
 void p2p_close(fdtd_b200_solver::PeerLink* link) {
@@ -1874,6 +1927,21 @@ int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st, bool stored_by_kernel
             CU_TRY(h, cudaMemcpyAsync(h->lower.mat + h->plane * h->lower.nzl * h->idx_bytes, h->mat, h->plane * h->idx_bytes, cudaMemcpyDeviceToDevice, st));
     }
     }
+    if (h->has_pml && h->lower.present && h->lower.psi_ghost) {
+        // ψ_H of my first plane → the slab below (it recomputes H' of that plane): the set that belongs to `set`'s fields, into
+        // the slot of the tick those fields belong to
+        const bool pending = set != h->cur_set;
+        uint64_t fp[3];
+        pml_first_plane(h, fp);
+        const size_t slot = 2 * (fp[0] + fp[1] + fp[2]);
+        float* dst = h->lower.psi_ghost + ((h->tick + (pending ? 1 : 0)) & 1) * slot;
+        for (int a = 0; a < 3; ++a) {
+            for (int g = 0; g < 2 && fp[a]; ++g)
+                CU_TRY(h, cudaMemcpyAsync(dst + g * fp[a], pending ? h->pml[a].psi_alt[g] : h->pml[a].psi[0][g], fp[a] * sizeof(float),
+                                          cudaMemcpyDeviceToDevice, st));
+            dst += 2 * fp[a];
+        }
+    }
     h->p2p_mat_sent = true;
     h->halo_seq += 1;
     if (h->upper.present) k_signal_flag<<<1, 1, 0, st>>>(h->upper.flags + 0, h->halo_seq);   // "received from below"
@@ -1900,11 +1968,22 @@ int fdtd_b200_p2p_connected(fdtd_b200_handle h) { return h && h->p2p ? 1 : 0; }
 int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob) {
     if (!h || !blob) return fail(h, FDTD_B200_EINVAL, "NULL argument");
     if (!h->fused) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport needs a fused-step handle (FDTD_B200_FUSED_STEP on an eligible lattice)");
-    if (h->has_pml) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport does not run the PML passes; use the two-kernel slab path");
+    if (h->has_pml && !h->pml_in_kernel) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport carries a PML only inside the fused kernel (fdtd_b200_pml_in_kernel); use the two-kernel slab path");
     if (int rc = set_device(h)) return rc;
     if (!h->d_flags) {
         CU_TRY(h, cudaMalloc(&h->d_flags, 64));
         CU_TRY(h, cudaMemset(h->d_flags, 0, 64));
+    }
+    // receive buffer for ψ_H of the plane above this slab (the x and y profiles are global, the z entry exists if that plane is a PML coordinate)
+    if (h->psi_ghost) { cudaFree(h->psi_ghost); h->psi_ghost = nullptr; }
+    h->ghost_plane[0] = h->ghost_plane[1] = h->ghost_plane[2] = 0;
+    if (h->has_pml && h->z_end < h->nz) {
+        h->ghost_plane[0] = static_cast<size_t>(h->pml[0].n) * h->ny;
+        h->ghost_plane[1] = static_cast<size_t>(h->pml[1].n) * h->nx;
+        h->ghost_plane[2] = h->pml[2].ghost ? h->nx * h->ny : 0;
+        const size_t floats = std::max<size_t>(4 * (h->ghost_plane[0] + h->ghost_plane[1] + h->ghost_plane[2]), 1);
+        CU_TRY(h, cudaMalloc(&h->psi_ghost, floats * sizeof(float)));
+        CU_TRY(h, cudaMemset(h->psi_ghost, 0, floats * sizeof(float)));
     }
     P2PBlob b;
     std::memset(&b, 0, sizeof b);
@@ -1921,6 +2000,12 @@ int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob) {
     b.raw_flags = reinterpret_cast<uint64_t>(h->d_flags);
     CU_TRY(h, cudaIpcGetMemHandle(&b.mat, h->mat));
     CU_TRY(h, cudaIpcGetMemHandle(&b.flags, h->d_flags));
+    if (h->psi_ghost) {
+        b.raw_psi_ghost = reinterpret_cast<uint64_t>(h->psi_ghost);
+        CU_TRY(h, cudaIpcGetMemHandle(&b.psi_ghost, h->psi_ghost));
+    }
+    for (int a = 0; a < 3; ++a) b.ghost_plane[a] = h->ghost_plane[a];
+    if (h->has_pml) pml_first_plane(h, b.first_plane);
     std::memset(blob, 0, FDTD_B200_P2P_BLOB_BYTES);
     std::memcpy(blob, &b, sizeof b);
     return FDTD_B200_OK;
@@ -1944,6 +2029,15 @@ int fdtd_b200_p2p_connect(fdtd_b200_handle h, const void* lower_blob, const void
         if (b.nx != h->nx || b.ny != h->ny || b.nz != h->nz || b.idx_bytes != static_cast<uint32_t>(h->idx_bytes))
             return fail(h, FDTD_B200_EINVAL, "neighbour blob describes a different lattice");
         if (side == 0 ? b.z_end != h->z_begin : b.z_begin != h->z_end) return fail(h, FDTD_B200_EINVAL, "neighbour slab is not adjacent");
+        {   // both sides must have been given the same PML: what the upper slab pushes is what the lower one expects
+            uint64_t mine[3] = {0, 0, 0};
+            if (h->has_pml) pml_first_plane(h, mine);
+            for (int a = 0; a < 3; ++a) {
+                const uint64_t expect = side == 0 ? b.ghost_plane[a] : h->ghost_plane[a];
+                const uint64_t sent = side == 0 ? mine[a] : b.first_plane[a];
+                if (expect != sent) return fail(h, FDTD_B200_EINVAL, "the neighbour slab was given a different PML (set the same profiles on every slab before fdtd_b200_p2p_export)");
+            }
+        }
         if (int rc = p2p_open(h, b, side == 0 ? &h->lower : &h->upper)) return rc;
     }
     if (!h->bstream) {
@@ -1977,7 +2071,7 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
     // default: the boundary CTAs store into the neighbours' ghost planes themselves; FDTD_B200_P2P_COPY_ENGINE=1 selects
     // the earlier variant (seven peer cudaMemcpyAsync per step and cut after the boundary kernels) for comparison
     static const bool copy_engine = [] { const char* e = std::getenv("FDTD_B200_P2P_COPY_ENGINE"); return e && e[0] == '1'; }();
-    const bool in_kernel = !copy_engine;
+    const bool in_kernel = !copy_engine && !h->has_pml;   // the PML instantiation has no PUSH variant: its planes go by copy engine with the ψ planes
     // whatever was enqueued on the main stream before (uploads, earlier steps, a refresh) precedes the first boundary launch
     CU_TRY(h, cudaEventRecord(h->ev_main, S));
     for (uint64_t s = 0; s < n_steps; ++s) {

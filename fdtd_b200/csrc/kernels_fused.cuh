@@ -68,6 +68,9 @@ struct FusedPmlView {
     const float2* bc_e[3];     // … E half-step
     const float* gh_in[3][2];  // ψ_H of the current set: G_ab, G_ac   layouts: x [z][y][k], y [z][k][x], z [k][y][x]
     float* gh_out[3][2];       // ψ_H of the pending set
+    // z-slabs with a neighbour above: ψ_H of that neighbour's first plane (the recomputed plane nz), received into a
+    // separate buffer; the pointers are biased so that the index of plane nz (axis z: of slab entry n[2]) lands in it
+    const float* gh_ghost[3][2];
     float* ge[3][2];           // ψ_E
 };
 
@@ -171,20 +174,20 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         static_assert(!PML || (BY >= 4 && 4 * BX == 128), "the first four warps scan the tile's 128 columns");
         if (tid < 4 * BX) {
             const int gx = x0 + tid;
-            if (Q.n[0] && gx < V.nx) x_k = __ldg(Q.map[0] + gx);
+            if (Q.map[0] != nullptr && gx < V.nx) x_k = __ldg(Q.map[0] + gx);
             const unsigned m = __ballot_sync(0xffffffffu, x_k >= 0);
             x_rank = __popc(m & ((1u << lane) - 1u));
             if (lane == 0) S.wcnt[tid >> 5] = __popc(m);
         }
         if (tid < BY) {
             const int gy = y0 + tid;
-            const int ky = (Q.n[1] && gy < V.ny) ? __ldg(Q.map[1] + gy) : -1;
+            const int ky = (Q.map[1] != nullptr && gy < V.ny) ? __ldg(Q.map[1] + gy) : -1;
             S.yk[tid] = ky;
             if (ky >= 0) { S.ybc[0][tid] = __ldg(Q.bc_h[1] + ky); S.ybc[1][tid] = __ldg(Q.bc_e[1] + ky); }
         }
         for (int t = tid; t <= n && t < PS::ZMAX; t += NT) {
             const int z = za + t;
-            const int kz = (Q.n[2] && z < V.nz) ? __ldg(Q.map[2] + z) : -1;
+            const int kz = (Q.map[2] != nullptr && (z < V.nz || (z == V.nz && V.hi_open))) ? __ldg(Q.map[2] + z) : -1;   // map[nz]: the neighbour's plane
             S.zk[t] = kz;
             if (kz >= 0) { S.zbc[0][t] = __ldg(Q.bc_h[2] + kz); S.zbc[1][t] = __ldg(Q.bc_e[2] + kz); }
         }
@@ -268,8 +271,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const int kx = S.xk[lane];
                 if (kk < n_h) {
                     const size_t qi = (static_cast<size_t>(za + kk) * V.ny + y) * Q.n[0] + kx;
-                    cp_async4(&S.xs[kk & 1][0][0][ty][lane], Q.gh_in[0][0] + qi);
-                    cp_async4(&S.xs[kk & 1][0][1][ty][lane], Q.gh_in[0][1] + qi);
+                    const bool ghost = za + kk == V.nz;
+                    cp_async4(&S.xs[kk & 1][0][0][ty][lane], (ghost ? Q.gh_ghost[0][0] : Q.gh_in[0][0]) + qi);
+                    cp_async4(&S.xs[kk & 1][0][1][ty][lane], (ghost ? Q.gh_ghost[0][1] : Q.gh_in[0][1]) + qi);
                 }
                 if (kk >= 1 && ty < LO::CORE_ROWS) {
                     const size_t qi = (static_cast<size_t>(za + kk - 1) * V.ny + y) * Q.n[0] + kx;
@@ -294,7 +298,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         if (PML && act) {
             // the y- and z-slab ψ of the next iteration's quads (plain float4 loads there): pull the lines into L2 now
             const int kk = k + 1, pky = S.yk[ty];
-            const bool nh = kk < n_h, ne = ty < LO::CORE_ROWS && kk <= n;
+            const bool nh = kk < n_h && za + kk < V.nz, ne = ty < LO::CORE_ROWS && kk <= n;
             if (pky >= 0) {
                 const size_t q0 = (static_cast<size_t>(za + kk - 1) * Q.n[1] + pky) * sy + x, dq = static_cast<size_t>(Q.n[1]) * sy;
                 if (nh) { prefetch_l2(Q.gh_in[1][0] + q0 + dq); prefetch_l2(Q.gh_in[1][1] + q0 + dq); }
@@ -419,9 +423,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     // y and z slabs (whole rows / planes: warp- and CTA-uniform): G ← b·G + c·∂E/∂x_a from the staged planes
                     // again, H_b += d_b·G_ac, H_c −= d_b·G_ab; y before z as the passes run (k_pml_axis<0, 1>, <0, 2>)
                     const int pky = ok ? S.yk[r] : -1, pkz = ok ? S.zk[k] : -1;
+                    const bool ghost_h = zk == V.nz;   // the plane above a z-slab: the upper neighbour's ψ_H, read-only here
                     if (pky >= 0) {
                         const size_t qy = (static_cast<size_t>(zk) * Q.n[1] + pky) * sy + gx;
-                        const float4 a = ld4(Q.gh_in[1][0] + qy), b = ld4(Q.gh_in[1][1] + qy);
+                        const float4 a = ld4((ghost_h ? Q.gh_ghost[1][0] : Q.gh_in[1][0]) + qy), b = ld4((ghost_h ? Q.gh_ghost[1][1] : Q.gh_in[1][1]) + qy);
                         const float2 bc = S.ybc[0][r];
                         float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
@@ -439,7 +444,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     }
                     if (pkz >= 0) {
                         const size_t qz = (static_cast<size_t>(pkz) * V.ny + gy) * sy + gx;
-                        const float4 a = ld4(Q.gh_in[2][0] + qz), b = ld4(Q.gh_in[2][1] + qz);
+                        const float4 a = ld4((ghost_h ? Q.gh_ghost[2][0] : Q.gh_in[2][0]) + qz), b = ld4((ghost_h ? Q.gh_ghost[2][1] : Q.gh_in[2][1]) + qz);
                         const float2 bc = S.zbc[0][k];
                         float g0[4] = {a.x, a.y, a.z, a.w}, g1[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
@@ -508,12 +513,12 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     const int ky = S.yk[r], kz = S.zk[k];
                     if (ky >= 0) {
                         const float2 bc = S.ybc[0][r];
-                        const float g1 = fmaf(bc.x, Q.gh_in[1][1][(static_cast<size_t>(zk) * Q.n[1] + ky) * sy + gx], bc.y * dex_dy);
+                        const float g1 = fmaf(bc.x, (zk == V.nz ? Q.gh_ghost[1][1] : Q.gh_in[1][1])[(static_cast<size_t>(zk) * Q.n[1] + ky) * sy + gx], bc.y * dex_dy);
                         hz1 = fmaf(c.w, g1, hz1);
                     }
                     if (kz >= 0) {
                         const float2 bc = S.zbc[0][k];
-                        const float g0 = fmaf(bc.x, Q.gh_in[2][0][(static_cast<size_t>(kz) * V.ny + gy) * sy + gx], bc.y * dex_dz);
+                        const float g0 = fmaf(bc.x, (zk == V.nz ? Q.gh_ghost[2][0] : Q.gh_in[2][0])[(static_cast<size_t>(kz) * V.ny + gy) * sy + gx], bc.y * dex_dz);
                         hy1 = fmaf(-c.w, g0, hy1);
                     }
                 }

@@ -29,3 +29,14 @@ def test_two_ranks_with_cpml_bit_identical_to_one(b200):
            "--master-port", "29572", os.path.join(ROOT, "tools", "slab_parity.py"), "64,48,40", "25", "1", "0", "nccl", "6"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout and "pml=6" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
+
+
+def test_two_ranks_with_cpml_inside_the_fused_kernel_over_peer_memory(b200):
+    """Fused z-slabs with the CPML advanced inside the step kernel; ψ_H of each slab's first plane travels to the slab below
+    with the boundary planes (CUDA IPC peer memory).  Bit-identical to the single-domain two-kernel run with the slab passes."""
+    if b200.lib().fdtd_b200_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29573", os.path.join(ROOT, "tools", "slab_parity.py"), "128,48,40", "25", "1", "1", "p2p", "6"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout and "pml=6" in res.stdout and "fused=True" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]

@@ -124,6 +124,54 @@ def test_pml_layers_the_fused_tiling_cannot_hold_fall_back_to_the_passes(b200):
         assert np.array_equal(a.read_field(comp), f.read_field(comp))
 
 
+@pytest.mark.parametrize("size,cuts,thickness", [
+    ((128, 16, 24), (9,), 5),            # the cut lies outside the z layers
+    ((128, 16, 24), (3, 21), 5),         # both cuts run through a z layer: the plane above a slab is a PML plane
+    ((256, 10, 12), (1, 3, 10), 4),      # one- and two-plane slabs (no interior launch), four slabs
+])
+def test_pml_on_fused_slabs_over_the_peer_memory_transport_equals_one_domain(b200, size, cuts, thickness):
+    """Fused z-slabs with the CPML inside the kernel (fdtd_b200_p2p_*; all slab handles in one process on one GPU): every
+    slab recomputes H' of the plane above it and needs that plane's ψ_H, which the upper slab pushes with its boundary
+    planes.  Bit-identical to the whole-domain fused run, including sources and probes in the layers, and after a reset."""
+    w = _with_pml(b200, _random_workload(b200, size, seed=sum(size) + len(cuts), dx=(1.0, 1.0, 1.0), dt=0.25), thickness)
+    nz = size[2]
+    w.sources.append(((2, 1, cuts[0]), b200.GaussianPulse(0.2, 0.5).with_amplitudes((1, 2, 3), (-1, 0.5, 2))))
+    probes = [(1, 1, cuts[0] - 1), (3, 2, cuts[0]), (size[0] - 1, size[1] - 1, nz - 1), (size[0] // 2, size[1] // 2, nz // 2)]
+    init = random_fields(w, seed=6)
+    steps = 7
+    tab = w.source_table(steps)
+    bounds = list(zip((0,) + tuple(cuts), tuple(cuts) + (nz,)))
+    _, whole, s_whole = b200_run(b200, w, steps, exact=True, init=init, probes=probes, fused=True)
+    assert whole.pml_in_kernel()
+    slabs = []
+    for a, b in bounds:
+        st = b200.FdtdB200Backend(exact_arithmetic=True, fused_step=True, z_slab=(a, b)).create_instance(w.solver_config(), w.domain()).create_state()
+        assert st.uses_fused and st.has_pml() and st.pml_in_kernel()
+        slabs.append(st)
+    blobs = [st.p2p_export() for st in slabs]
+    for k, st in enumerate(slabs):
+        st.p2p_connect(blobs[k - 1] if k > 0 else None, blobs[k + 1] if k + 1 < len(slabs) else None)
+    for rnd in range(2):
+        for st, (a, b) in zip(slabs, bounds):
+            if rnd:
+                st.reset()
+            st.write_field(b200.FieldComponent.E, init[0][a:b], (0, 0, a), (size[0], size[1], b))
+            st.write_field(b200.FieldComponent.H, init[1][a:b], (0, 0, a), (size[0], size[1], b))
+            st.register_probes(probes)
+            st.set_source_table(w.source_points(), tab)
+        for st in slabs:
+            st.p2p_refresh()
+        for _ in range(steps):
+            for st in slabs:
+                st.p2p_step(1)
+        for st in slabs:
+            st.sync()
+        for comp in (b200.FieldComponent.E, b200.FieldComponent.H):
+            got = np.concatenate([st.read_field(comp) for st in slabs], axis=0)
+            assert np.array_equal(got, whole.read_field(comp)), (rnd, comp)
+        assert np.array_equal(sum(st.read_probes(0, steps) for st in slabs), s_whole)
+
+
 def test_pml_on_two_slabs_equals_one_domain(b200):
     from fdtd_b200 import _lib as L
 
@@ -214,11 +262,16 @@ def test_pml_state_reset_checkpoint_and_errors(b200, tmp_path):
     ptr = nan.ctypes.data_as(L._dp)
     with pytest.raises(L.Fdtd_b200Error):
         L.check(st._lib.fdtd_b200_set_pml(st._h, 0, ptr, ptr, None, None), st._h)
-    # fused slab handles cannot carry a PML (their halo protocol recomputes H' of the neighbour's plane without ψ)
+    # fused slab handles carry the PML inside the kernel only; ψ_H of the plane above the slab arrives over the peer-memory
+    # transport, so stepping the slab's last plane without it is refused, and so are layers the kernel's tiling cannot hold
     slab = b200.FdtdB200Backend(fused_step=True, z_slab=(0, 5)).create_instance(w2.solver_config(), w2.domain()).create_state()
-    if slab.uses_fused:
-        with pytest.raises(L.Fdtd_b200Error):
-            slab.set_pml(w.pml)
+    assert slab.uses_fused
+    slab.set_pml(w.pml)
+    assert slab.has_pml() and slab.pml_in_kernel()
+    with pytest.raises(L.Fdtd_b200Error):
+        slab.fused_update(0, 5)
+    with pytest.raises(L.Fdtd_b200Error):
+        slab.set_pml(b200.PmlProfiles.graded(w.solver_config(), 20, b200.GradedPml(), axes=(0,)))
     del dp
 
 

@@ -23,7 +23,7 @@ def main():
     overlap = (sys.argv[3] != "0") if len(sys.argv) > 3 else True
     fused = (sys.argv[4] != "0") if len(sys.argv) > 4 else False
     transport = sys.argv[5] if len(sys.argv) > 5 else "nccl"     # nccl | p2p (NVLink peer memory, fused handles only)
-    pml = int(sys.argv[6]) if len(sys.argv) > 6 else 0            # CPML cells per face (two-kernel handles)
+    pml = int(sys.argv[6]) if len(sys.argv) > 6 else 0            # CPML cells per face (two-kernel handles over NCCL, or fused handles over p2p: DESIGN §4b)
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     zb, ze = partition_z(lattice[2], world)[rank]
