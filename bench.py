@@ -347,6 +347,9 @@ def run_b200(args) -> None:
     if n_gpus == 1 and not args.no_cpu_baseline:
         cb = time_cpu_reference(lattice, args.cpu_planes, args.cpu_steps, 2)
         cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        # SURVEY §8d's second row: one thread ≙ FdtdCpuBackend::single_threaded (cpu/mod.rs:187-193), on a smaller sample
+        c1 = time_cpu_reference(lattice, max(args.cpu_planes // 4, 2), max(args.cpu_steps // 2, 2), 1, threads=1)
+        cpu_baseline["single_thread"] = {k: c1[k] for k in ("value", "unit", "cores", "sample")}
     out = {"metric": "Yee cell-updates/sec", "value": value, "unit": "Gcells/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
            "ms_per_step": ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": f"heterogeneous {nx}x{ny}x{nz} lattice (64 balls of 4 material kinds) inside the 16-cell graded lossy layer, "

@@ -293,9 +293,12 @@ int fdtd_b200_halo_copy(fdtd_b200_handle dst, int which_dst, fdtd_b200_handle sr
 int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob /* FDTD_B200_P2P_BLOB_BYTES */);
 /* lower_blob / upper_blob: blobs of the ranks owning the slab below / above (NULL where the lattice ends). */
 int fdtd_b200_p2p_connect(fdtd_b200_handle h, const void* lower_blob, const void* upper_blob);
-/* Push the CURRENT boundary planes (and, once, the material index of the first plane) into the neighbours' ghost planes
- * — after connect, reset and after fields were written from outside.  Asynchronous: ordered against the neighbours' steps by
- * the same device-side flags, so no host barrier is needed as long as every rank calls it at the same point. */
+/* Push the CURRENT boundary planes (and, once, the material index of the first plane; with a PML also psi_H of the first
+ * plane, into the lower neighbour's receive slot of the current tick's parity) into the neighbours' ghost planes — after
+ * connect, reset, fdtd_b200_set_time, fdtd_b200_write_pml_state and after fields were written from outside.  Asynchronous:
+ * ordered against the neighbours' steps by the same device-side flags, so no host barrier is needed as long as every rank
+ * calls it at the same point.  (fdtd_b200_p2p_export allocates the psi receive buffer: export again, and re-connect the
+ * neighbours, after changing the PML.) */
 int fdtd_b200_p2p_refresh(fdtd_b200_handle h);
 int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps);
 /* 1 when connect succeeded and p2p_step may be called. */
