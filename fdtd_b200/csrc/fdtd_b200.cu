@@ -64,6 +64,18 @@ struct fdtd_b200_solver {
     uint32_t n_src = 0;
     uint64_t src_rows = 0, src_row = 0;
     size_t src_cells_cap = 0, src_vals_cap = 0;
+    // per-step protocol (one update pass = set_sources → step(1) → read_probes, runner.rs:522-526) without host round trips:
+    // the step's forcing row goes through a ring of pinned slots by cudaMemcpyAsync in stream order (no synchronize while
+    // the cell set is unchanged), and a one-step fdtd_b200_step mirrors its probe row into pinned host memory
+    static constexpr int PIN_SLOTS = 8;
+    std::vector<long long> src_cells_host;   // what d_src_cells holds
+    float* pin_src = nullptr;                // [PIN_SLOTS][pin_src_floats]
+    size_t pin_src_floats = 0;
+    cudaEvent_t pin_src_ev[PIN_SLOTS] = {};
+    int pin_src_next = 0;
+    float* pin_probe = nullptr;              // [PIN_SLOTS][n_probes_total * 6]
+    uint64_t pin_probe_tick[PIN_SLOTS] = {}; // tick + 1 of the row a slot mirrors (0: none)
+    size_t pin_probe_floats = 0;
 
     // probes
     long long* d_probe_cells = nullptr;
@@ -759,6 +771,28 @@ void commit_fused(fdtd_b200_handle h) {
             for (int g = 0; g < 2; ++g) std::swap(h->pml[a].psi[0][g], h->pml[a].psi_alt[g]);
 }
 
+void probe_mirror_invalidate(fdtd_b200_handle h) {
+    for (auto& t : h->pin_probe_tick) t = 0;
+}
+
+// one-step protocol: the probe row of the step just enqueued follows its kernel into pinned host memory without a host
+// round trip; fdtd_b200_read_probes of exactly that tick then only waits for the stream
+int probe_mirror_row(fdtd_b200_handle h, uint64_t tick) {
+    const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
+    if (row == 0 || !h->d_probe_ring) return FDTD_B200_OK;
+    if (h->pin_probe_floats < row) {
+        if (h->pin_probe) { CU_TRY(h, cudaStreamSynchronize(h->stream)); cudaFreeHost(h->pin_probe); h->pin_probe = nullptr; h->pin_probe_floats = 0; }
+        CU_TRY(h, cudaMallocHost(&h->pin_probe, sizeof(float) * row * fdtd_b200_solver::PIN_SLOTS));
+        h->pin_probe_floats = row;
+        probe_mirror_invalidate(h);
+    }
+    const int slot = static_cast<int>(tick % fdtd_b200_solver::PIN_SLOTS);
+    CU_TRY(h, cudaMemcpyAsync(h->pin_probe + slot * h->pin_probe_floats, h->d_probe_ring + (tick % h->ring_steps) * row, row * sizeof(float),
+                              cudaMemcpyDeviceToHost, h->stream));
+    h->pin_probe_tick[slot] = tick + 1;
+    return FDTD_B200_OK;
+}
+
 void end_step(fdtd_b200_handle h) {
     h->tick += 1;
     h->time += h->cfg.dt;  // accumulated (cpu/mod.rs:513), never tick*dt
@@ -1025,6 +1059,9 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_probe_cells) cudaFree(h->d_probe_cells);
     if (h->d_probe_slot) cudaFree(h->d_probe_slot);
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
+    if (h->pin_src) cudaFreeHost(h->pin_src);
+    if (h->pin_probe) cudaFreeHost(h->pin_probe);
+    for (auto& ev : h->pin_src_ev) if (ev) cudaEventDestroy(ev);
     if (h->d_stage) cudaFree(h->d_stage);
     for (int a = 0; a < 3; ++a) pml_free_axis(h, a);
     if (h->psi_ghost) cudaFree(h->psi_ghost);
@@ -1062,6 +1099,7 @@ int fdtd_b200_reset(fdtd_b200_handle h) {
     h->tick = 0;
     h->time = 0.0;
     h->probe_first_tick = 0;
+    probe_mirror_invalidate(h);
     return FDTD_B200_OK;
 }
 
@@ -1101,6 +1139,7 @@ int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time) {
     h->time = time;
     h->n_src = 0; h->src_rows = 0; h->src_row = 0;
     h->probe_first_tick = tick;
+    probe_mirror_invalidate(h);
     return FDTD_B200_OK;
 }
 
@@ -1342,6 +1381,32 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
         for (uint32_t q = 0; q < m; ++q)
             std::memcpy(&vals[(s * m + q) * 6], values + (s * n_src + kept[q].second) * 6, 6 * sizeof(float));
 
+    // per-step fast path: same cell set as the table on the device → only the values move, asynchronously.  The copy is
+    // ordered after every enqueued kernel that reads the old row (same stream; p2p_step joins its boundary stream back into
+    // it), and the pinned slot is reused only after its own copy has completed.
+    if (n_steps == 1 && h->d_src_cells && lc == h->src_cells_host && h->src_vals_cap >= vals.size()) {
+        if (h->pin_src_floats < vals.size()) {
+            CU_TRY(h, cudaStreamSynchronize(h->stream));
+            if (h->pin_src) { cudaFreeHost(h->pin_src); h->pin_src = nullptr; h->pin_src_floats = 0; }
+            const size_t cap = std::max<size_t>(vals.size(), 96);
+            CU_TRY(h, cudaMallocHost(&h->pin_src, sizeof(float) * cap * fdtd_b200_solver::PIN_SLOTS));
+            h->pin_src_floats = cap;
+            for (auto& ev : h->pin_src_ev)
+                if (!ev) CU_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        }
+        const int slot = h->pin_src_next;
+        h->pin_src_next = (slot + 1) % fdtd_b200_solver::PIN_SLOTS;
+        CU_TRY(h, cudaEventSynchronize(h->pin_src_ev[slot]));   // a never-recorded event is complete
+        float* p = h->pin_src + static_cast<size_t>(slot) * h->pin_src_floats;
+        std::memcpy(p, vals.data(), sizeof(float) * vals.size());
+        CU_TRY(h, cudaMemcpyAsync(h->d_src_vals, p, sizeof(float) * vals.size(), cudaMemcpyHostToDevice, h->stream));
+        CU_TRY(h, cudaEventRecord(h->pin_src_ev[slot], h->stream));
+        h->n_src = m;
+        h->src_rows = 1;
+        h->src_row = 0;
+        return FDTD_B200_OK;
+    }
+    h->src_cells_host.clear();
     if (h->src_cells_cap < m) {
         if (h->d_src_cells) cudaFree(h->d_src_cells);
         h->d_src_cells = nullptr; h->src_cells_cap = 0;
@@ -1358,6 +1423,7 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     CU_TRY(h, cudaMemcpy(h->d_src_cells, lc.data(), sizeof(long long) * m, cudaMemcpyHostToDevice));
     CU_TRY(h, cudaMemcpy(h->d_src_vals, vals.data(), sizeof(float) * vals.size(), cudaMemcpyHostToDevice));
+    h->src_cells_host = lc;
     h->n_src = m;
     h->src_rows = n_steps;
     h->src_row = 0;
@@ -1413,6 +1479,7 @@ int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
         }
         end_step(h);
     }
+    if (n_steps == 1 && h->n_probes_total) return probe_mirror_row(h, h->tick - 1);
     return FDTD_B200_OK;
 }
 
@@ -1570,6 +1637,7 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
     if (h->d_probe_ring) { cudaFree(h->d_probe_ring); h->d_probe_ring = nullptr; }
     h->n_probes_total = 0; h->n_probes_local = 0;
     h->probe_first_tick = h->tick;
+    probe_mirror_invalidate(h);
     if (n == 0) return FDTD_B200_OK;
     if (!cells) return fail(h, FDTD_B200_EINVAL, "NULL cells");
     const uint64_t n_global = h->plane * h->nz;
@@ -1606,6 +1674,10 @@ int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_st
     if (int rc = set_device(h)) return rc;
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
+    if (n_steps == 1 && h->pin_probe && h->pin_probe_tick[first_tick % fdtd_b200_solver::PIN_SLOTS] == first_tick + 1) {
+        std::memcpy(out, h->pin_probe + (first_tick % fdtd_b200_solver::PIN_SLOTS) * h->pin_probe_floats, row * sizeof(float));
+        return FDTD_B200_OK;
+    }
     uint64_t done = 0;
     while (done < n_steps) {
         const uint64_t r = (first_tick + done) % h->ring_steps;

@@ -420,3 +420,44 @@ def test_full_size_matches_oracle_on_a_short_run(b200, oracle):
     assert rel_l2(st.read_field(b200.FieldComponent.E), ref64.field(oracle.E)) <= TOL_VS_F64
     assert rel_l2(st.read_field(b200.FieldComponent.H), ref64.field(oracle.H)) <= TOL_VS_F64
     assert rel_l2(series, s64) <= TOL_VS_F64
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_per_step_protocol_equals_the_batched_run(b200, fused):
+    """set_sources -> step(1) -> read_probes every step (runner.rs:522-526; the forcing row travels through the pinned ring
+    without a synchronize, the probe row comes back through the pinned mirror) == set_source_table + step(n), bit for bit;
+    a changed cell set, a step without forcing and a late re-read of an old tick take the synchronous paths."""
+    w = _random_workload(b200, (128, 16, 12), seed=5)
+    probes = [(64, 8, 6), (0, 0, 0), (127, 15, 11), (65, 8, 6)]
+    n = 24
+    _, ref, ref_series = b200_run(b200, w, n, exact=True, probes=probes, fused=fused)
+    inst, st = b200_state(b200, w, exact=True, fused=fused)
+    assert st.uses_fused == fused
+    st.register_probes(probes)
+    table = w.source_table(n)
+    pts = w.source_points()
+    rows = []
+    for s in range(n):
+        up = inst.begin_update(st)
+        for k, p in enumerate(pts):
+            up.set_forcing(p, b200.SourceValues(tuple(table[s, k, :3]), tuple(table[s, k, 3:])))
+        up.finish()
+        rows.append(st.read_probes(s, 1)[0])
+    assert np.array_equal(np.stack(rows), ref_series)
+    assert np.array_equal(st.read_probes(n - 20, 20), ref_series[n - 20:])       # older ticks: from the device ring
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.read_field(b200.FieldComponent.E))
+    assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.read_field(b200.FieldComponent.H))
+    # another cell set, then none, then the first one again, then both
+    other = (3, 2, 1)
+    vals = np.array([1.0, 2.0, -3.0, 0.5, 0.0, 0.25], dtype=np.float32)
+    for step_pts in ([other], [], pts, pts + [other]):
+        up = inst.begin_update(st)
+        for p in step_pts:
+            up.set_forcing(p, b200.SourceValues(tuple(vals[:3]), tuple(vals[3:])))
+        up.finish()
+        if step_pts:
+            ref.set_source_table(step_pts, np.tile(vals, (1, len(step_pts), 1)))
+        ref.step(1)
+        assert np.array_equal(st.read_probes(st.tick() - 1, 1), ref.read_probes(ref.tick() - 1, 1))
+    assert st.tick() == ref.tick() == n + 4
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.read_field(b200.FieldComponent.E))
