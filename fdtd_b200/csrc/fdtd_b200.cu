@@ -29,6 +29,7 @@ struct Tune {
     int bx = 0, by = 0, zc = 0;  // 0 = choose automatically
     int variant = -1;            // -1 auto | 0 register-streaming kernels | 1 TMA bulk-copy staged kernels
     int stages = 0;              // ring depth of the staged kernels (0 = default)
+    int table_smem = 0;          // fused step: largest coefficient table staged in shared memory (0 = default)
 };
 
 }  // namespace
@@ -52,6 +53,7 @@ struct fdtd_b200_solver {
     bool fused = false;
     FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
     bool fused_maps_ready = false;
+    int sm_smem_bytes = 0, sm_smem_reserved = 0;   // shared memory per SM / reserved per CTA (queried at the first fused launch)
     int cur_set = 0;                // which buffer set f[] currently points at
     void* mat = nullptr;
     int idx_bytes = 1;
@@ -185,8 +187,8 @@ bool c_or_d(double perm, double sigma, double dt, double* a, double* b) {
 Tune parse_tune() {
     Tune t;
     if (const char* s = std::getenv("FDTD_B200_TUNE")) {
-        int a = 0, b = 0, c = 0, d = -1, e = 0;
-        if (std::sscanf(s, "%d,%d,%d,%d,%d", &a, &b, &c, &d, &e) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; }
+        int a = 0, b = 0, c = 0, d = -1, e = 0, f = 0;
+        if (std::sscanf(s, "%d,%d,%d,%d,%d,%d", &a, &b, &c, &d, &e, &f) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; t.table_smem = f; }
     }
     return t;
 }
@@ -465,7 +467,26 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     FusedView V{};
     for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
     V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table);
-    V.table_in_smem = ((pml && sizeof(IdxT) == 1) || h->n_table <= 64) ? 1 : 0;   // the PML instantiation assumes it for 8-bit indices (≤ 256 rows = 4 KB)
+    // The coefficient table is staged in shared memory as long as two CTAs still fit on an SM (≈ 1060 rows with 8-bit
+    // indices, ≈ 1000 with 16-bit ones); larger tables are read through L1.  Measured at 512³ (tools/many_materials.py,
+    // profiles/r01_many_materials.jsonl): 65–256 materials 127.4 Gcells/s from shared memory against 101–119 through L1.
+    uint32_t table_smem_max = 64;
+    {
+        if (h->sm_smem_bytes == 0) {
+            if (cudaDeviceGetAttribute(&h->sm_smem_bytes, cudaDevAttrMaxSharedMemoryPerMultiprocessor, h->device) != cudaSuccess ||
+                cudaDeviceGetAttribute(&h->sm_smem_reserved, cudaDevAttrReservedSharedMemoryPerBlock, h->device) != cudaSuccess) {
+                (void)cudaGetLastError();
+                h->sm_smem_bytes = -1;
+            }
+        }
+        const int sm_bytes = h->sm_smem_bytes, reserved = h->sm_smem_reserved;
+        if (sm_bytes > 0) {
+            const long long room = sm_bytes / 2 - reserved - static_cast<long long>(LO::smem_bytes(0, pml));
+            if (room > 0) table_smem_max = std::max<uint32_t>(table_smem_max, static_cast<uint32_t>(room / static_cast<long long>(sizeof(float4))));
+        }
+    }
+    if (h->tune.table_smem > 0) table_smem_max = static_cast<uint32_t>(h->tune.table_smem);
+    V.table_in_smem = ((pml && sizeof(IdxT) == 1) || h->n_table <= table_smem_max) ? 1 : 0;   // the PML instantiation assumes it for 8-bit indices (≤ 256 rows = 4 KB)
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
     V.z_lo = z_lo; V.z_hi = z_hi;
     V.lo_open = h->z_begin > 0 ? 1 : 0;

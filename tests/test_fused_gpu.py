@@ -227,3 +227,26 @@ def test_p2p_argument_errors(b200, tune):
         a.p2p_connect(None, None)                            # a neighbour blob is required above
     with pytest.raises(L.Fdtd_b200Error):
         a.p2p_connect(None, b"\0" * L.P2P_BLOB_BYTES)
+
+
+@pytest.mark.parametrize("n_materials,limit", [(200, 0), (300, 0), (1500, 0), (300, 64)])
+def test_fused_step_with_large_coefficient_tables(b200, oracle, tune, n_materials, limit):
+    """Coefficient table staged in shared memory as long as two CTAs fit on an SM (8- and 16-bit indices), read through
+    L1 beyond that (and when FDTD_B200_TUNE caps it): bit-identical to the fp32 oracle either way."""
+    from fdtd_b200 import configs
+
+    tune(f"0,0,0,-1,0,{limit}")
+    size = (256, 12, 9)
+    rng = np.random.default_rng(n_materials)
+    pal = [b200.Material.VACUUM] + [b200.Material(1.0 + 0.01 * k, 0.001 * (k % 5), 1.0 + 0.002 * (k % 11), 0.0005 * (k % 3)) for k in range(1, n_materials)]
+    ids = rng.integers(0, n_materials, size[0] * size[1] * size[2]).astype(np.uint32)
+    ids[:n_materials] = np.arange(n_materials, dtype=np.uint32)
+    src = b200.ContinousWave(0.3, 0.07).with_amplitudes((1.0, -2.0, 3.0), (0.5, 0.25, -0.125))
+    w = configs.Workload("tables", size, b200.Resolution((1.0, 0.5, 2.0), 0.2), b200.PhysicalConstants.REDUCED, pal, ids,
+                         [((128, 6, 4), src)], [], 0)
+    init = random_fields(w, seed=2)
+    ref, _ = oracle_run(oracle, w, 6, oracle.F32, init=init)
+    st, _ = run(b200, w, 6, exact=True, fused=True, init=init)
+    assert st.uses_fused
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
+    assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.field(oracle.H).astype(np.float32))
