@@ -39,6 +39,24 @@ __device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* m
                  : "memory");
 }
 
+__device__ __forceinline__ void tma_load_3d_hint(void* dst_smem, const CUtensorMap* map, int x, int y, int z, uint64_t* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3, %4}], [%5], %6;" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(map), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)), "l"(policy)
+                 : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+// Field stores of the step are streaming (st.global.cs: written once, next read a whole lattice later) and the staged planes
+// are fetched with an L2 evict_last policy, so that the halo rows / columns a neighbouring CTA re-reads a moment later stay
+// in L2 while the write stream passes through.  Measured at 512³ on one box, alternating (tools/exp_hints.sh,
+// profiles/r01_exp_cache_hints.txt): plain/plain 1.0704 ms, streaming stores 1.0721, evict_last loads 1.0604, both 1.0575;
+// evict_first loads 1.30 ms (the halo re-reads go to HBM).
+__device__ __forceinline__ void stg4(float* p, const float4& v) { __stcs(reinterpret_cast<float4*>(p), v); }
+
 struct FusedView {
     const float* in[6];   // Ex Ey Ez Hx Hy Hz of the current step (plane 0)
     float* out[6];        // the other buffer set
@@ -221,6 +239,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const int last_h_plane = (zb < V.nz || V.hi_open != 0) ? zb : zb - 1;   // H'/old-E planes za..last_h_plane are needed
     const int n_h = last_h_plane - za + 1;                          // number of H-plane iterations with a phase A
 
+    const uint64_t ld_policy = l2_policy_evict_last();
     // ---- producer: one lane of the last warp issues 7 tensor copies per plane ------------------------------------
     auto issue_e = [&](int plane, int slot) {
         if (lane == 0) {
@@ -228,7 +247,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             mbar_arrive_expect_tx(bar, 3u * LO::E_BOX_BYTES);
             float* s = reinterpret_cast<float*>(e_slots + static_cast<size_t>(slot) * LO::E_SLOT_BYTES);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * E_COMP, &M.e[c], x0 - 4, y0 - 1, plane + 1, bar);
+            for (int c = 0; c < 3; ++c) tma_load_3d_hint(s + c * E_COMP, &M.e[c], x0 - 4, y0 - 1, plane + 1, bar, ld_policy);
         }
     };
     auto issue_h = [&](int plane, int slot) {
@@ -238,7 +257,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             unsigned char* sl = h_slots + static_cast<size_t>(slot) * LO::H_SLOT_BYTES;
             float* s = reinterpret_cast<float*>(sl);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tma_load_3d(s + c * H_COMP, &M.h[c], x0 - 4, y0, plane + 1, bar);
+            for (int c = 0; c < 3; ++c) tma_load_3d_hint(s + c * H_COMP, &M.h[c], x0 - 4, y0, plane + 1, bar, ld_policy);
             tma_load_3d(sl + 3 * H_COMP * 4, &M.mat, x0, y0, plane, bar);
         }
     };
@@ -472,7 +491,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     mk_cur[0] = mk[0]; mk_cur[1] = mk[1]; mk_cur[2] = mk[2]; mk_cur[3] = mk[3];
                     if (core && k < n) {                          // this CTA owns H' of its core rows and planes
                         const size_t gi = static_cast<size_t>(zk) * sz + static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
-                        st4(V.out[3] + gi, hx); st4(V.out[4] + gi, hy); st4(V.out[5] + gi, hz);
+                        stg4(V.out[3] + gi, hx); stg4(V.out[4] + gi, hy); stg4(V.out[5] + gi, hz);
                         if (PUSH && zk == 0 && V.push_down[3] != nullptr) {
                             const size_t pi = static_cast<size_t>(gy) * sy + static_cast<size_t>(gx);
                             st4(V.push_down[3] + pi, hx); st4(V.push_down[4] + pi, hy);
@@ -653,7 +672,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             ez = make_float4(ezv[0], ezv[1], ezv[2], ezv[3]);
             if (core) {
                 const size_t gi = static_cast<size_t>(zp) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
-                st4(V.out[0] + gi, ex); st4(V.out[1] + gi, ey); st4(V.out[2] + gi, ez);
+                stg4(V.out[0] + gi, ex); stg4(V.out[1] + gi, ey); stg4(V.out[2] + gi, ez);
                 if (PUSH) {
                     const size_t pi = static_cast<size_t>(y) * sy + static_cast<size_t>(x);
                     if (zp == 0 && V.push_down[0] != nullptr) { st4(V.push_down[0] + pi, ex); st4(V.push_down[1] + pi, ey); st4(V.push_down[2] + pi, ez); }
