@@ -30,6 +30,7 @@ struct Tune {
     int variant = -1;            // -1 auto | 0 register-streaming kernels | 1 TMA bulk-copy staged kernels
     int stages = 0;              // ring depth of the staged kernels (0 = default)
     int table_smem = 0;          // fused step: largest coefficient table staged in shared memory (0 = default)
+    int l2_promotion = 0;        // fused step: L2 promotion of the tensor maps (0 = default 256 B, 1 none, 2 64 B, 3 128 B)
 };
 
 }  // namespace
@@ -187,8 +188,8 @@ bool c_or_d(double perm, double sigma, double dt, double* a, double* b) {
 Tune parse_tune() {
     Tune t;
     if (const char* s = std::getenv("FDTD_B200_TUNE")) {
-        int a = 0, b = 0, c = 0, d = -1, e = 0, f = 0;
-        if (std::sscanf(s, "%d,%d,%d,%d,%d,%d", &a, &b, &c, &d, &e, &f) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; t.table_smem = f; }
+        int a = 0, b = 0, c = 0, d = -1, e = 0, f = 0, g = 0;
+        if (std::sscanf(s, "%d,%d,%d,%d,%d,%d,%d", &a, &b, &c, &d, &e, &f, &g) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; t.table_smem = f; t.l2_promotion = g; }
     }
     return t;
 }
@@ -441,8 +442,13 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
     const cuuint64_t strides[2] = {h->nx * elem, h->nx * h->ny * elem};
     const cuuint32_t box[3] = {bx, by, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
+    // 256-byte promotion measured best (tools/exp_promo.sh, 512³: 1.0388 ms against 1.0450 with 128 B or none, 1.0470 with 64 B;
+    // 1024×1024×128: 1.0558 against 1.0670)
+    const CUtensorMapL2promotion promo = h->tune.l2_promotion == 1 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                                         : h->tune.l2_promotion == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                         : h->tune.l2_promotion == 3 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
     const CUresult r = enc(out, dt, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                           promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(h, FDTD_B200_ECUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r)));
     return FDTD_B200_OK;
 }
