@@ -362,7 +362,7 @@ def run_b200(args) -> None:
                                   "Gaussian point source, 8 probes (BASELINE configs[2]; " + ("the same lattice for every N: strong scaling, BASELINE configs[3])" if args.scaling == "strong" else "weak-scaled 512^3 cells per GPU for N>1)"),
                       "lattice": [nx, ny, nz], "cells_per_gpu": cells_total // n_gpus, "decomposition": f"z-slabs x{n_gpus}",
                       "l2": f"working set {49 if st.uses_fused else 25} B/cell x {cells_total // n_gpus / 1e6:.0f}M cells per GPU >> 126 MB L2 (no flush needed)",
-                      "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport,
+                      "row_pitch": st.row_pitch, "arithmetic": "exact" if args.exact else "fast", "step_kernel": "fused single pass (ping-pong buffers)" if st.uses_fused else "two half-step kernels (in place)", "halo_overlap": bool(world > 1 and not args.no_overlap), "halo_transport": transport,
                       **({"cpml_cells_per_face": args.pml, "cpml": "inside the fused step kernel" if st.pml_in_kernel() else "psi passes over the slabs after the step kernel(s); kernel times include them",
                          "cpml_psi_bytes_per_step": psi_bytes} if args.pml else {})},
            "roofline": roofline, "cpu_baseline": cpu_baseline,

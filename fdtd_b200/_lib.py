@@ -123,6 +123,7 @@ SYMBOLS = {
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_write_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_device_field": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p)]),
+    "fdtd_b200_row_pitch": (C.c_uint64, [_H]),
     "fdtd_b200_register_probes": (C.c_int, [_H, C.c_uint32, _u64p]),
     "fdtd_b200_read_probes": (C.c_int, [_H, C.c_uint64, C.c_uint64, _fp]),
     "fdtd_b200_project": (C.c_int, [_H, C.c_int, _fp, _fp, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]),

@@ -37,7 +37,16 @@ struct Tune {
 
 struct fdtd_b200_solver {
     fdtd_b200_config cfg{};
-    uint64_t nx = 0, ny = 0, nz = 0;   // global
+    uint64_t nx = 0, ny = 0, nz = 0;   // global; nx is the ROW PITCH of every array (fields, index, y/z-slab ψ, halo planes)
+    // Row padding: lattices whose nx is not a multiple of 16 would miss the float4 / TMA kernels (16-byte rows of every stream,
+    // the index bytes included), and the reference derives nx from ceil(size/dx) (fdtd/mod.rs:24-29), so most user lattices are
+    // unaligned.  Such handles store rows of nx = nxl rounded up cells; the nx - nxl pad cells of a row index an extra all-zero
+    // coefficient row (table entry pad_id), so they stay exactly 0, and the x+1 Neumann test of the E half-step is made against
+    // nxl.  Every cell index that crosses the ABI (sources, probes, boxes, material ids, projection, PML profiles) is in terms
+    // of the caller's nxl-wide lattice and converted here.
+    uint64_t nxl = 0;                  // the caller's nx
+    uint32_t pad_id = 0;               // table row of the pad cells (only when nx != nxl)
+    uint32_t n_table_user = 0;         // table rows the caller supplied
     uint64_t z_begin = 0, z_end = 0;   // slab
     uint64_t nzl = 0;                  // owned planes
     uint64_t plane = 0;                // nx*ny
@@ -208,6 +217,7 @@ LatticeView lattice_view(fdtd_b200_handle h) {
     L.n_table = static_cast<int>(h->n_table);
     L.table_in_smem = h->n_table <= 4096 ? 1 : 0;
     L.nx = static_cast<int>(h->nx); L.ny = static_cast<int>(h->ny); L.nz = static_cast<int>(h->nzl);
+    L.nxl = static_cast<int>(h->nxl);
     L.lo_open = h->z_begin > 0 ? 1 : 0;
     L.hi_open = h->z_end < h->nz ? 1 : 0;
     for (int a = 0; a < 3; ++a) {
@@ -415,9 +425,18 @@ bool use_bulk(fdtd_b200_handle h) {
 
 
 // ---- fused single-pass step (kernels_fused.cuh) --------------------------------------------------------
-bool fused_eligible(const fdtd_b200_config& cfg, uint64_t nzl, int idx_bytes, bool vec4) {
-    (void)nzl;
-    return vec4 && (cfg.nx * idx_bytes) % 16 == 0 && cfg.nx >= 128;
+bool fused_eligible(uint64_t pitch, int idx_bytes, bool vec4) {
+    return vec4 && (pitch * idx_bytes) % 16 == 0 && pitch >= 128;
+}
+
+// Row pitch of a lattice of nx cells per row (see fdtd_b200_solver::nxl).  Rows of at least 64 cells are padded to the next
+// multiple of 16 (≤ 23 % more bytes), 97..127 cells to 128 (the fused kernel's tile); FDTD_B200_NO_ROW_PADDING=1 or the
+// generic-kernel flag keep the caller's nx, and so does a table that has no room for the pad row.
+uint64_t row_pitch(uint64_t nx, uint32_t flags, uint32_t n_table) {
+    if (nx % 16 == 0 || nx < 64 || (flags & FDTD_B200_FORCE_GENERIC_KERNELS) || n_table >= 65536) return nx;
+    if (const char* e = std::getenv("FDTD_B200_NO_ROW_PADDING")) if (e[0] == '1') return nx;
+    if (nx > 96 && nx < 128) return 128;
+    return (nx + 15) / 16 * 16;
 }
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -494,6 +513,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     if (h->tune.table_smem > 0) table_smem_max = static_cast<uint32_t>(h->tune.table_smem);
     V.table_in_smem = ((pml && sizeof(IdxT) == 1) || h->n_table <= table_smem_max) ? 1 : 0;   // the PML instantiation assumes it for 8-bit indices (≤ 256 rows = 4 KB)
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
+    V.nxl = static_cast<int>(h->nxl);
     V.z_lo = z_lo; V.z_hi = z_hi;
     V.lo_open = h->z_begin > 0 ? 1 : 0;
     V.hi_open = h->z_end < h->nz ? 1 : 0;
@@ -532,8 +552,10 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     dim3 block(BX, BY, 1);
     dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0, pml);
-    auto k = pml ? k_step_fused<EXACT, IdxT, BX, BY, false, true>
-                 : (push ? k_step_fused<EXACT, IdxT, BX, BY, true, false> : k_step_fused<EXACT, IdxT, BX, BY, false, false>);
+    const bool xpad = h->nxl != h->nx;
+    auto k = pml ? (xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, true, true> : k_step_fused<EXACT, IdxT, BX, BY, false, true, false>)
+                 : (push ? (xpad ? k_step_fused<EXACT, IdxT, BX, BY, true, false, true> : k_step_fused<EXACT, IdxT, BX, BY, true, false, false>)
+                         : (xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, false, true> : k_step_fused<EXACT, IdxT, BX, BY, false, false, false>));
     if (push) {   // boundary planes of the peer-memory transport: results also go into the neighbours' pending-set ghost planes
         const int pend = h->cur_set ^ 1;
         if (h->lower.present)
@@ -729,7 +751,7 @@ int prof_begin(fdtd_b200_handle h, int which, int planes) {
     CU_TRY(h, cudaEventCreate(&a));
     CU_TRY(h, cudaEventCreate(&b));
     h->prof_events[which].emplace_back(a, b);
-    h->prof_cells[which] += static_cast<uint64_t>(planes) * h->plane;
+    h->prof_cells[which] += static_cast<uint64_t>(planes) * h->nxl * h->ny;   // lattice cells (pad cells are not work)
     CU_TRY(h, cudaEventRecord(a, h->stream));
     return FDTD_B200_OK;
 }
@@ -866,7 +888,10 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
 
     auto* h = new fdtd_b200_solver();
     h->cfg = *cfg;
-    h->nx = cfg->nx; h->ny = cfg->ny; h->nz = cfg->nz;
+    h->nxl = cfg->nx; h->ny = cfg->ny; h->nz = cfg->nz;
+    h->nx = row_pitch(cfg->nx, cfg->flags, n_table);
+    h->n_table_user = n_table;
+    if (h->nx != h->nxl) { h->pad_id = n_table; n_table += 1; }
     h->z_begin = cfg->z_begin;
     h->z_end = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
     h->nzl = h->z_end - h->z_begin;
@@ -903,7 +928,7 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
         h->f[c] = h->alloc[c] + h->plane;
     }
     h->fused = ((cfg->flags & FDTD_B200_FUSED_STEP) || h->tune.variant == 2) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
-               fused_eligible(h->cfg, h->nzl, h->idx_bytes, h->vec4);
+               fused_eligible(h->nx, h->idx_bytes, h->vec4);
     if (h->fused) {
         for (int c = 0; c < 6; ++c) {
             CU_NEW(cudaMalloc(&h->alt_alloc[c], comp_floats * sizeof(float)));
@@ -914,15 +939,25 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
     // material index (+8 bytes slack so the last quad's vector load never leaves the allocation)
     CU_NEW(cudaMalloc(&h->mat, (h->n_local + h->plane) * h->idx_bytes + 16));
     CU_NEW(cudaMemsetAsync(h->mat, 0, (h->n_local + h->plane) * h->idx_bytes + 16, h->stream));
+    if (h->nx != h->nxl) {   // pad cells (also of the plane above the slab) → the all-zero coefficient row
+        const size_t rows = static_cast<size_t>(h->ny) * (h->nzl + 1);
+        const int blocks = static_cast<int>(std::min<size_t>((rows * (h->nx - h->nxl) + 255) / 256, 148 * 8));
+        if (h->idx_bytes == 1) k_fill_pad_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(static_cast<uint8_t*>(h->mat), h->nxl, h->nx, rows, h->pad_id);
+        else k_fill_pad_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(static_cast<uint16_t*>(h->mat), h->nxl, h->nx, rows, h->pad_id);
+        h->launches += 1;
+        CU_NEW(cudaGetLastError());
+    }
     if (material_ids) {
-        // stream the u32 ids through a bounded staging buffer and narrow them on the device
-        const size_t chunk = std::min<size_t>(h->n_local, size_t(1) << 24);
+        // stream the u32 ids (rows of nxl cells) through a bounded staging buffer and narrow them on the device into the pitched rows
+        const size_t n_cells = static_cast<size_t>(h->nxl) * h->ny * h->nzl;
+        const size_t rows_per_chunk = std::max<size_t>(1, (size_t(1) << 24) / h->nxl);
+        const size_t chunk = std::min<size_t>(n_cells, rows_per_chunk * h->nxl);
         uint32_t* d_ids = nullptr;
         CU_NEW(cudaMalloc(&d_ids, chunk * sizeof(uint32_t)));
-        for (size_t off = 0; off < h->n_local; off += chunk) {
-            const size_t n = std::min(chunk, static_cast<size_t>(h->n_local) - off);
+        for (size_t off = 0; off < n_cells; off += chunk) {
+            const size_t n = std::min(chunk, n_cells - off);
             for (size_t i = 0; i < n; ++i) {
-                if (material_ids[off + i] >= n_table) {
+                if (material_ids[off + i] >= h->n_table_user) {
                     cudaFree(d_ids);
                     h->err = "material id out of range of the palette/table";
                     return bail(FDTD_B200_EINVAL);
@@ -931,8 +966,9 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
             cudaError_t e = cudaMemcpyAsync(d_ids, material_ids + off, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream);
             if (e == cudaSuccess) {
                 const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 148 * 8));
-                if (h->idx_bytes == 1) k_narrow_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint8_t*>(h->mat) + off, n);
-                else k_narrow_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint16_t*>(h->mat) + off, n);
+                const size_t row0 = off / h->nxl;   // chunks are whole rows
+                if (h->idx_bytes == 1) k_narrow_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint8_t*>(h->mat) + row0 * h->nx, n, h->nxl, h->nx);
+                else k_narrow_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(d_ids, static_cast<uint16_t*>(h->mat) + row0 * h->nx, n, h->nxl, h->nx);
                 h->launches += 1;
                 e = cudaStreamSynchronize(h->stream);
             }
@@ -942,18 +978,25 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
     }
     CU_NEW(cudaMalloc(&h->table, sizeof(float4) * n_table));
     static_assert(sizeof(fdtd_b200_coefficients_f32) == sizeof(float4), "table entry is four floats");
-    CU_NEW(cudaMemcpyAsync(h->table, table, sizeof(float4) * n_table, cudaMemcpyHostToDevice, h->stream));
+    CU_NEW(cudaMemsetAsync(h->table, 0, sizeof(float4) * n_table, h->stream));   // the pad row, if any, is all zeros
+    CU_NEW(cudaMemcpyAsync(h->table, table, sizeof(float4) * h->n_table_user, cudaMemcpyHostToDevice, h->stream));
     CU_NEW(cudaStreamSynchronize(h->stream));
 #undef CU_NEW
     *out = h;
     return FDTD_B200_OK;
 }
 
+// A cell index of the caller's lattice (x + nxl·(y + ny·z)) → the index of the same cell in the pitched arrays.
+uint64_t pitched_cell(fdtd_b200_handle h, uint64_t c) {
+    if (h->nx == h->nxl) return c;
+    return (c / h->nxl) * h->nx + c % h->nxl;
+}
+
 // global box → local BoxView; EINVAL when empty or outside slab
 int make_box(fdtd_b200_handle h, const uint64_t lo[3], const uint64_t hi[3], BoxView* B, size_t* n_cells) {
     if (!lo || !hi) return fail(h, FDTD_B200_EINVAL, "box bounds are NULL");
     uint64_t l[3], u[3];
-    const uint64_t dims[3] = {h->nx, h->ny, h->nz};
+    const uint64_t dims[3] = {h->nxl, h->ny, h->nz};
     for (int a = 0; a < 3; ++a) {
         l[a] = std::min(lo[a], dims[a]);
         u[a] = std::min(std::max(hi[a], lo[a]), dims[a]);  // util.rs:157-160: end = max(start, end)
@@ -1043,11 +1086,12 @@ size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_byt
     if (!validate_cfg(cfg, &why) || (index_bytes != 1 && index_bytes != 2)) return 0;
     const uint64_t ze = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
     const uint64_t nzl = ze - cfg->z_begin;
-    const uint64_t plane = cfg->nx * cfg->ny;
+    const uint64_t pitch = row_pitch(cfg->nx, cfg->flags, index_bytes == 1 ? 1 : 65535);
+    const uint64_t plane = pitch * cfg->ny;
     // 6 fp32 components with two ghost planes each + the material index (cf. 136 B/cell cpu/mod.rs:217-221,
     // 80 B/cell wgpu/mod.rs:129-133)
     const bool fused = (cfg->flags & FDTD_B200_FUSED_STEP) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
-                       fused_eligible(*cfg, nzl, static_cast<int>(index_bytes), cfg->nx % 4 == 0);
+                       fused_eligible(pitch, static_cast<int>(index_bytes), pitch % 4 == 0);
     return static_cast<size_t>((fused ? 12 : 6) * sizeof(float) * plane * (nzl + 2) + plane * (nzl + 1) * index_bytes + 16);
 }
 
@@ -1201,7 +1245,7 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
     pml_free_axis(h, axis);
     if (!b_e) return FDTD_B200_OK;  // cleared
     if (!b_h) { b_h = b_e; c_h = c_e; }
-    const uint64_t ext = axis == 0 ? h->nx : (axis == 1 ? h->ny : h->nz);
+    const uint64_t ext = axis == 0 ? h->nxl : (axis == 1 ? h->ny : h->nz);   // the caller's profile length
     const uint64_t lo = axis == 2 ? h->z_begin : 0, hi = axis == 2 ? h->z_end : ext;
     auto& A = h->pml[axis];
     std::vector<float2> bc_h, bc_e;
@@ -1239,7 +1283,7 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
         }
     std::vector<int> map;
     if (h->fused) {   // the fused kernel's PML instantiation: ψ_H ping-pong set and the coordinate → k map (+ the plane above a slab)
-        map.assign(static_cast<size_t>(hi - lo) + (above ? 1 : 0), -1);
+        map.assign(static_cast<size_t>(axis == 0 ? h->nx : hi - lo) + (above ? 1 : 0), -1);   // axis x: one entry per cell of the pitch
         for (int k = 0; k < A.n; ++k) map[static_cast<size_t>(A.pos[k])] = k;
         if (A.ghost) map[static_cast<size_t>(hi - lo)] = A.n;
         if ((e = cudaMalloc(&A.d_map, sizeof(int) * map.size())) != cudaSuccess) return oom(e);
@@ -1296,6 +1340,7 @@ int fdtd_b200_write_pml_state(fdtd_b200_handle h, const float* in) { return pml_
 uint64_t fdtd_b200_tick(fdtd_b200_handle h) { return h ? h->tick : 0; }
 double fdtd_b200_time(fdtd_b200_handle h) { return h ? h->time : 0.0; }
 int fdtd_b200_index_bytes(fdtd_b200_handle h) { return h ? h->idx_bytes : 0; }
+uint64_t fdtd_b200_row_pitch(fdtd_b200_handle h) { return h ? h->nx : 0; }
 int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
 int fdtd_b200_uses_bulk(fdtd_b200_handle h) { return h && use_bulk(h) ? 1 : 0; }
 int fdtd_b200_uses_fused(fdtd_b200_handle h) { return h && h->fused ? 1 : 0; }
@@ -1350,14 +1395,17 @@ int fdtd_b200_timer_stop(fdtd_b200_handle h, double* elapsed_ms) {
 int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out) {
     if (!h || !ids_out) return fail(h, FDTD_B200_EINVAL, "NULL argument");
     if (int rc = set_device(h)) return rc;
-    const size_t chunk = std::min<size_t>(h->n_local, size_t(1) << 24);
+    const size_t n_cells = static_cast<size_t>(h->nxl) * h->ny * h->nzl;   // the caller's lattice: rows of nxl ids
+    const size_t rows_per_chunk = std::max<size_t>(1, (size_t(1) << 24) / h->nxl);
+    const size_t chunk = std::min<size_t>(n_cells, rows_per_chunk * h->nxl);
     uint32_t* d = nullptr;
     CU_TRY(h, cudaMalloc(&d, chunk * sizeof(uint32_t)));
-    for (size_t off = 0; off < h->n_local; off += chunk) {
-        const size_t n = std::min(chunk, static_cast<size_t>(h->n_local) - off);
+    for (size_t off = 0; off < n_cells; off += chunk) {
+        const size_t n = std::min(chunk, n_cells - off);
         const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 148 * 8));
-        if (h->idx_bytes == 1) k_widen_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint8_t*>(h->mat) + off, d, n);
-        else k_widen_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint16_t*>(h->mat) + off, d, n);
+        const size_t row0 = off / h->nxl;
+        if (h->idx_bytes == 1) k_widen_ids<uint8_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint8_t*>(h->mat) + row0 * h->nx, d, n, h->nxl, h->nx);
+        else k_widen_ids<uint16_t><<<blocks, 256, 0, h->stream>>>(static_cast<const uint16_t*>(h->mat) + row0 * h->nx, d, n, h->nxl, h->nx);
         h->launches += 1;
         cudaError_t e = cudaMemcpyAsync(ids_out + off, d, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
@@ -1369,10 +1417,10 @@ int fdtd_b200_read_material_ids(fdtd_b200_handle h, uint32_t* ids_out) {
 
 int fdtd_b200_read_coefficient_table(fdtd_b200_handle h, fdtd_b200_coefficients_f32* out, uint32_t cap, uint32_t* n_out) {
     if (!h || !n_out) return fail(h, FDTD_B200_EINVAL, "NULL argument");
-    *n_out = h->n_table;
+    *n_out = h->n_table_user;   // without the pad row of padded lattices
     if (!out || cap == 0) return FDTD_B200_OK;
     if (int rc = set_device(h)) return rc;
-    const uint32_t n = std::min(cap, h->n_table);
+    const uint32_t n = std::min(cap, h->n_table_user);
     CU_TRY(h, cudaMemcpyAsync(out, h->table, sizeof(float4) * n, cudaMemcpyDeviceToHost, h->stream));
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     return FDTD_B200_OK;
@@ -1384,10 +1432,16 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
     if (n_src == 0 || n_steps == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; return FDTD_B200_OK; }
     if (!cells || !values) return fail(h, FDTD_B200_EINVAL, "NULL cells/values");
-    const uint64_t n_global = h->plane * h->nz;
+    const uint64_t n_global = h->nxl * h->ny * h->nz;
     for (uint32_t k = 0; k < n_src; ++k)
         if (cells[k] >= n_global) return fail(h, FDTD_B200_EINVAL, "set_forcing called with invalid point (cell index outside the lattice)");
     if (int rc = set_device(h)) return rc;
+    std::vector<uint64_t> pitched;
+    if (h->nx != h->nxl) {   // padded rows: the kernels look cells up by their index in the pitched arrays
+        pitched.resize(n_src);
+        for (uint32_t k = 0; k < n_src; ++k) pitched[k] = pitched_cell(h, cells[k]);
+        cells = pitched.data();
+    }
 
     // keep the slab's cells; for duplicates the later column wins (cpu/mod.rs:399-408); sort by local index
     const uint64_t base = h->z_begin * h->plane;
@@ -1667,12 +1721,13 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
     probe_mirror_invalidate(h);
     if (n == 0) return FDTD_B200_OK;
     if (!cells) return fail(h, FDTD_B200_EINVAL, "NULL cells");
-    const uint64_t n_global = h->plane * h->nz;
+    const uint64_t n_global = h->nxl * h->ny * h->nz;
     const uint64_t base = h->z_begin * h->plane;
     std::vector<std::pair<long long, int>> loc;
     for (uint32_t k = 0; k < n; ++k) {
         if (cells[k] >= n_global) return fail(h, FDTD_B200_EINVAL, "probe cell outside the lattice");
-        if (cells[k] >= base && cells[k] < base + h->n_local) loc.emplace_back(static_cast<long long>(cells[k] - base), static_cast<int>(k));
+        const uint64_t c = pitched_cell(h, cells[k]);
+        if (c >= base && c < base + h->n_local) loc.emplace_back(static_cast<long long>(c - base), static_cast<int>(k));
     }
     std::sort(loc.begin(), loc.end());
     // the fused sampler writes one slot per distinct cell; duplicates are resolved on readback
@@ -1728,6 +1783,7 @@ int fdtd_b200_project(fdtd_b200_handle h, int component, const float projection[
     ProjectView V{};
     V.fx = h->f[c0]; V.fy = h->f[c0 + 1]; V.fz = h->f[c0 + 2];
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz_global = static_cast<int>(h->nz);
+    V.nxl = static_cast<int>(h->nxl);
     V.z_begin = static_cast<int>(h->z_begin); V.nz_local = static_cast<int>(h->nzl);
     std::memcpy(V.proj, projection, sizeof V.proj);
     std::memcpy(V.cmap, color_map, sizeof V.cmap);
@@ -1827,6 +1883,7 @@ int scene_upload(fdtd_b200_handle h, const uint64_t dims[3], const double m[16],
     for (int i = 0; i < 12; ++i) V->m[i] = m[i];
     V->shapes = dev->shapes; V->boxes = dev->boxes; V->n_shapes = static_cast<int>(n);
     V->nx = static_cast<int>(dims[0]); V->ny = static_cast<int>(dims[1]);
+    V->pitch = V->nx;
     return FDTD_B200_OK;
 }
 
@@ -1887,17 +1944,18 @@ int fdtd_b200_rasterize_scene(int device, const uint64_t dims[3], uint64_t z_beg
 int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_to_world[16], const fdtd_b200_shape* shapes,
                                        uint32_t n_shapes, uint32_t default_label) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "handle is NULL");
-    const uint64_t dims[3] = {h->nx, h->ny, h->nz};
+    const uint64_t dims[3] = {h->nxl, h->ny, h->nz};
     std::string why;
     if (int rc = scene_validate(dims, solver_to_world, shapes, n_shapes, &why)) return fail(h, rc, why);
-    if (default_label >= h->n_table) return fail(h, FDTD_B200_EINVAL, "default label out of range of the palette/table");
+    if (default_label >= h->n_table_user) return fail(h, FDTD_B200_EINVAL, "default label out of range of the palette/table");
     for (uint32_t i = 0; i < n_shapes; ++i)
-        if (shapes[i].label >= h->n_table) return fail(h, FDTD_B200_EINVAL, "shape label out of range of the palette/table");
+        if (shapes[i].label >= h->n_table_user) return fail(h, FDTD_B200_EINVAL, "shape label out of range of the palette/table");
     CU_TRY(h, cudaSetDevice(h->device));
     SceneDevice dev;
     SceneView V{};
     if (int rc = scene_upload(h, dims, solver_to_world, shapes, n_shapes, h->stream, &dev, &V)) return rc;
     V.default_label = default_label;
+    V.pitch = static_cast<int>(h->nx);   // pad cells keep the pad row's id
     V.z0 = static_cast<long long>(h->z_begin);
     // the index buffer keeps one plane above the slab (the fused step recomputes H' there); fill it when it exists globally
     V.n_planes = static_cast<long long>(h->nzl + (h->z_end < h->nz ? 1 : 0));

@@ -18,7 +18,9 @@ struct LatticeView {
     const float4* table;  // (c_a, c_b, d_a, d_b) per material, fp32
     int n_table;
     int table_in_smem;    // 1: kernels stage the table in shared memory (n_table small enough)
-    int nx, ny, nz;       // local dims (nz = owned planes)
+    int nx, ny, nz;       // local dims (nz = owned planes); nx is the row pitch of every array
+    int nxl;              // cells of a row that belong to the lattice (nxl ≤ nx; cells nxl..nx-1 are pad cells whose material is
+                          // the all-zero coefficient row, so they stay 0; only the x+1 Neumann test needs to know them)
     int lo_open, hi_open; // a neighbouring slab exists below / above (ghost plane is valid)
     float dx[3];
     float inv_dx[3];
@@ -263,7 +265,8 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
     size_t i = static_cast<size_t>(za) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
 
     const bool y_in = y + 1 < L.ny;
-    const bool x_in = x + 4 < L.nx;  // the quad's last cell has an x+1 neighbour
+    const bool x_in = x + 4 < L.nx;  // a float4 to the right of the quad exists
+    const int xlim = L.nxl - 1 - x;  // cell k of the quad has an x+1 neighbour inside the lattice iff k < xlim
     float4 hx_c = ld4(L.hx + i), hy_c = ld4(L.hy + i);
 
     for (int z = za; z < zb; ++z, i += sz) {
@@ -300,7 +303,7 @@ k_update_e_vec4(const LatticeView L, const ForcingView F, const ProbeView P, con
         float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool xk_in = (k < 3) || x_in;
+            const bool xk_in = k < xlim;
             const float dhz_dy = y_in ? deriv<EXACT>(hzyp[k], hzv[k], L.dx[1], L.inv_dx[1]) : 0.f;
             const float dhx_dy = y_in ? deriv<EXACT>(hxyp[k], hxv[k], L.dx[1], L.inv_dx[1]) : 0.f;
             const float dhy_dz = z_in ? deriv<EXACT>(hyzp[k], hyv[k], L.dx[2], L.inv_dx[2]) : 0.f;
@@ -394,7 +397,7 @@ k_update_e_generic(const LatticeView L, const ForcingView F, const ProbeView P, 
     for (int z = z_lo + blockIdx.z; z < z_hi; z += gridDim.z) {
         const size_t i = static_cast<size_t>(z) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
         const float hx = L.hx[i], hy = L.hy[i], hz = L.hz[i];
-        const bool x_in = x + 1 < L.nx, y_in = y + 1 < L.ny, z_in = (z + 1 < L.nz) || (L.hi_open != 0);
+        const bool x_in = x + 1 < L.nxl, y_in = y + 1 < L.ny, z_in = (z + 1 < L.nz) || (L.hi_open != 0);
         const float dhz_dy = y_in ? deriv<EXACT>(L.hz[i + sy], hz, L.dx[1], L.inv_dx[1]) : 0.f;
         const float dhx_dy = y_in ? deriv<EXACT>(L.hx[i + sy], hx, L.dx[1], L.inv_dx[1]) : 0.f;
         const float dhy_dz = z_in ? deriv<EXACT>(L.hy[i + sz], hy, L.dx[2], L.inv_dx[2]) : 0.f;
@@ -460,15 +463,23 @@ __global__ void k_scatter_box(float* __restrict__ fx, float* __restrict__ fy, fl
     }
 }
 
+// Material ids cross the ABI as rows of `nxl` u32 values; on the device a row holds `pitch` ≥ nxl narrow entries (pad cells last).
 template <typename IdxT>
-__global__ void k_widen_ids(const IdxT* __restrict__ in, uint32_t* __restrict__ out, size_t n) {
+__global__ void k_widen_ids(const IdxT* __restrict__ in, uint32_t* __restrict__ out, size_t n, size_t nxl, size_t pitch) {
     for (size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; t < n; t += static_cast<size_t>(gridDim.x) * blockDim.x)
-        out[t] = in[t];
+        out[t] = in[(t / nxl) * pitch + t % nxl];
 }
 template <typename IdxT>
-__global__ void k_narrow_ids(const uint32_t* __restrict__ in, IdxT* __restrict__ out, size_t n) {
+__global__ void k_narrow_ids(const uint32_t* __restrict__ in, IdxT* __restrict__ out, size_t n, size_t nxl, size_t pitch) {
     for (size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; t < n; t += static_cast<size_t>(gridDim.x) * blockDim.x)
-        out[t] = static_cast<IdxT>(in[t]);
+        out[(t / nxl) * pitch + t % nxl] = static_cast<IdxT>(in[t]);
+}
+// the pad cells of `rows` rows → `id` (the all-zero coefficient row)
+template <typename IdxT>
+__global__ void k_fill_pad_ids(IdxT* __restrict__ out, size_t nxl, size_t pitch, size_t rows, uint32_t id) {
+    const size_t w = pitch - nxl, n = rows * w;
+    for (size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; t < n; t += static_cast<size_t>(gridDim.x) * blockDim.x)
+        out[(t / w) * pitch + nxl + t % w] = static_cast<IdxT>(id);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -476,7 +487,8 @@ __global__ void k_narrow_ids(const uint32_t* __restrict__ in, IdxT* __restrict__
 // ------------------------------------------------------------------------------------------------
 struct ProjectView {
     const float* fx; const float* fy; const float* fz;  // local plane 0 of the sampled field
-    int nx, ny, nz_global, z_begin, nz_local;
+    int nx, ny, nz_global, z_begin, nz_local;   // nx = row pitch
+    int nxl;                                    // lattice cells of a row (what the projection scales by)
     float proj[16];   // column-major
     float cmap[16];   // column-major
     int mode;
@@ -498,7 +510,7 @@ __global__ void k_project_rgba8(const ProjectView V, uchar4* __restrict__ out) {
         u = (static_cast<float>(px) + 0.5f) / static_cast<float>(V.w);
         v = 1.0f - (static_cast<float>(py) + 0.5f) / static_cast<float>(V.h);
     }
-    const int dims[3] = {V.nx, V.ny, V.nz_global};
+    const int dims[3] = {V.nxl, V.ny, V.nz_global};
     int p[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {

@@ -324,7 +324,7 @@ k_update_e_bulk(const LatticeView L, const ForcingView F, const ProbeView P, con
 
     size_t i = static_cast<size_t>(za) * sz + static_cast<size_t>(min(y, L.ny - 1)) * sy + static_cast<size_t>(min(x, L.nx - 4));
     const bool y_in = y + 1 < L.ny;
-    const bool x_in = x + 4 < L.nx;
+    const int xlim = L.nxl - 1 - x;   // cell k of the quad has an x+1 neighbour inside the lattice iff k < xlim (pad cells: kernels.cuh)
     const int ty = threadIdx.y, tx4 = 4 * threadIdx.x;
     float4 hx_c = make_float4(0.f, 0.f, 0.f, 0.f), hy_c = hx_c;
 
@@ -390,7 +390,7 @@ k_update_e_bulk(const LatticeView L, const ForcingView F, const ProbeView P, con
         float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool xk_in = (k < 3) || x_in;
+            const bool xk_in = k < xlim;
             const float dhz_dy = y_in ? deriv<EXACT>(hzyp[k], hzv[k], L.dx[1], L.inv_dx[1]) : 0.f;
             const float dhx_dy = y_in ? deriv<EXACT>(hxyp[k], hxv[k], L.dx[1], L.inv_dx[1]) : 0.f;
             const float dhy_dz = z_in ? deriv<EXACT>(hyzp[k], hyv[k], L.dx[2], L.inv_dx[2]) : 0.f;

@@ -63,7 +63,8 @@ struct FusedView {
     const void* mat;
     const float4* table;
     int n_table, table_in_smem;
-    int nx, ny, nz;       // nz = planes owned by this handle (z-slab)
+    int nx, ny, nz;       // nz = planes owned by this handle (z-slab); nx = row pitch
+    int nxl;              // lattice cells of a row (≤ nx; the rest are pad cells, kernels.cuh) — read by the XPAD instantiations
     int z_lo, z_hi;       // planes updated by this launch
     int lo_open, hi_open; // a neighbouring slab exists below / above: ghost planes -1 / nz hold its old fields
     float dx[3], inv_dx[3];
@@ -138,7 +139,9 @@ struct FusedLayout {
     }
 };
 
-template <int EXACT, typename IdxT, int BX, int BY, bool PUSH = false, bool PML = false>
+// XPAD: rows carry pad cells (nxl < nx, lattices whose nx is not a multiple of 16): the x+1 Neumann test of E' is made per cell
+// against nxl instead of per quad against the pitch; everything else is untouched (pad cells have all-zero coefficients).
+template <int EXACT, typename IdxT, int BX, int BY, bool PUSH = false, bool PML = false, bool XPAD = false>
 __global__ void __launch_bounds__(BX * BY, 2)
 k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const ForcingView F, const ProbeView P, const int zc, const FusedPmlView Q) {
     using LO = FusedLayout<IdxT, BX, BY>;
@@ -276,6 +279,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const int x = x0 + 4 * tx, y = y0 + ty;
     const bool act = (x < V.nx) && (y < V.ny);
     const bool core = act && (ty < LO::CORE_ROWS);                  // this thread owns E' of its quad
+    const int nx_cells = XPAD ? V.nxl : V.nx;                       // lattice cells of a row
+    const int xlim = nx_cells - 1 - x;                              // XPAD: cell q of the quad has an x+1 neighbour iff q < xlim
 
     float4 hxo = make_float4(0.f, 0.f, 0.f, 0.f), hyo = hxo, hzo = hxo;   // H'(z_k) of the own quad
     int mk_prev[4] = {0, 0, 0, 0};
@@ -590,7 +595,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 if (static_cast<int>(lane) < nxs && y < V.ny) {
                     const int xl = S.xl[lane];
                     const float* pj = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + xl;
-                    const bool in = x0 + xl + 1 < V.nx;
+                    const bool in = x0 + xl + 1 < nx_cells;
                     const float dhy = in ? deriv<EXACT>(pj[H_COMP + 1], pj[H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float dhz = in ? deriv<EXACT>(pj[2 * H_COMP + 1], pj[2 * H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
                     const float2 bc = S.xbc[1][lane];
@@ -605,7 +610,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             auto e_quad = [&](auto with_src) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const bool xq_in = (q < 3) || x_in;
+                const bool xq_in = XPAD ? (q < xlim) : ((q < 3) || x_in);
                 const float dhz_dy = deriv_masked<EXACT>(hzyp[q], hzv[q], V.dx[1], idy, y_in);
                 const float dhx_dy = deriv_masked<EXACT>(hxyp[q], hxv[q], V.dx[1], idy, y_in);
                 const float dhy_dz = deriv_masked<EXACT>(hyzp[q], hyv[q], V.dx[2], idz, z_in);

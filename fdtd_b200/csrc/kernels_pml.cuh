@@ -56,7 +56,7 @@ k_pml_axis(const LatticeView L, const PmlAxisView P, const float* __restrict__ s
     const size_t i = static_cast<size_t>(z) * sz + static_cast<size_t>(y) * sy + x;
     const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? sy : sz);
     const int coord = AXIS == 0 ? x : (AXIS == 1 ? y : z);
-    const int extent = AXIS == 0 ? L.nx : (AXIS == 1 ? L.ny : L.nz);
+    const int extent = AXIS == 0 ? L.nxl : (AXIS == 1 ? L.ny : L.nz);
     constexpr int B = (AXIS + 1) % 3, C = (AXIS + 2) % 3;
     const float* sb = B == 0 ? s0 : (B == 1 ? s1 : s2);
     const float* sc = C == 0 ? s0 : (C == 1 ? s1 : s2);
@@ -106,7 +106,7 @@ k_update_e_box(const LatticeView L, const ForcingView F, float* __restrict__ ox,
     for (int z = B.z0 + blockIdx.z; z < B.z1; z += gridDim.z) {
         const size_t i = static_cast<size_t>(z) * sz + static_cast<size_t>(y) * sy + static_cast<size_t>(x);
         const float hx = L.hx[i], hy = L.hy[i], hz = L.hz[i];
-        const bool x_in = x + 1 < L.nx, y_in = y + 1 < L.ny, z_in = (z + 1 < L.nz) || (L.hi_open != 0);
+        const bool x_in = x + 1 < L.nxl, y_in = y + 1 < L.ny, z_in = (z + 1 < L.nz) || (L.hi_open != 0);
         const float dhz_dy = y_in ? deriv<EXACT>(L.hz[i + sy], hz, L.dx[1], L.inv_dx[1]) : 0.f;
         const float dhx_dy = y_in ? deriv<EXACT>(L.hx[i + sy], hx, L.dx[1], L.inv_dx[1]) : 0.f;
         const float dhy_dz = z_in ? deriv<EXACT>(L.hy[i + sz], hy, L.dx[2], L.inv_dx[2]) : 0.f;

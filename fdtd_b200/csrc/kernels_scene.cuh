@@ -33,7 +33,8 @@ struct SceneView {
     const SceneBox* boxes;
     int n_shapes;
     uint32_t default_label;
-    int nx, ny;
+    int nx, ny;              // lattice cells per row, rows per plane
+    int pitch;               // entries per row of `out` (≥ nx; pad entries are left alone)
     long long z0;            // global z of local plane 0
     long long n_planes;      // planes to rasterise
 };
@@ -94,8 +95,8 @@ __global__ void __launch_bounds__(256) k_rasterize_scene(const SceneView V, OutT
             }
             lab[c] = l;
         }
-        const long long base = (static_cast<long long>(zl) * V.ny + y) * V.nx + x0;
-        if ((V.nx & 3) == 0) {   // whole quad inside the row and aligned: one vector store
+        const long long base = (static_cast<long long>(zl) * V.ny + y) * V.pitch + x0;
+        if (((V.nx | V.pitch) & 3) == 0) {   // whole quad inside the row and aligned: one vector store
             if constexpr (sizeof(OutT) == 1) {
                 *reinterpret_cast<uint32_t*>(out + base) = lab[0] | (lab[1] << 8) | (lab[2] << 16) | (lab[3] << 24);
                 continue;

@@ -559,6 +559,11 @@ class FdtdB200SolverState:
         L.check(self._lib.fdtd_b200_device_field(self._h, c, C.byref(p)), self._h)
         return int(p.value)
 
+    @property
+    def row_pitch(self) -> int:
+        """Cells per stored row (>= lattice[0]; include/fdtd_b200.h, fdtd_b200_row_pitch)."""
+        return int(self._lib.fdtd_b200_row_pitch(self._h))
+
     def read_field(self, component: int, lo: Optional[Point] = None, hi: Optional[Point] = None) -> np.ndarray:
         """float32 [bz, by, bx, 3] of the box [lo, hi) (default: this handle's whole slab)."""
         n = self.lattice

@@ -339,8 +339,18 @@ int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_t
 int fdtd_b200_read_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out);
 /* The inverse (≙ FieldMut, lib.rs:114-127): overwrite a box of E or H. */
 int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], const float* in);
-/* Raw device pointer of one scalar component c in 0..5 = Ex,Ey,Ez,Hx,Hy,Hz (first owned plane). */
+/* Raw device pointer of one scalar component c in 0..5 = Ex,Ey,Ez,Hx,Hy,Hz (first owned plane).  Cell (x, y, z) of the
+ * slab sits at float offset x + pitch·(y + ny·z) with pitch = fdtd_b200_row_pitch(h). */
 int fdtd_b200_device_field(fdtd_b200_handle h, int c, void** device_ptr);
+/* Cells per stored row.  The reference sizes its lattice as ceil(size/dx) (fdtd/mod.rs:24-29), so nx is rarely a multiple of
+ * 16; the float4 / TMA kernels need 16-byte rows of every array, so lattices with nx >= 64 and nx % 16 != 0 are stored with
+ * rows padded to the next multiple of 16 (97..127 → 128).  The pad cells index an internal all-zero coefficient row and stay
+ * 0; they never influence a lattice cell (the x+1 boundary rule is applied at the caller's nx).  Everything that crosses this
+ * ABI — linear cell indices of sources and probes, boxes, material ids, PML profiles, projections, the coefficient table —
+ * is in terms of the caller's nx × ny × nz lattice; the pitch shows only in fdtd_b200_device_field, in the halo planes
+ * (fdtd_b200_halo_plane: pitch·ny floats), in fdtd_b200_memory_required and in the opaque PML state.  Setting the
+ * environment variable FDTD_B200_NO_ROW_PADDING=1 disables the padding (pitch == nx). */
+uint64_t fdtd_b200_row_pitch(fdtd_b200_handle h);
 
 /* Probe sampling fused into the E half-step: after every step, E and H of each registered cell
  * (global linear index) are appended to a device ring.  Re-registering clears the ring. */
