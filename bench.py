@@ -111,7 +111,7 @@ def build_workload(lattice, z_begin, z_end):
     nx, ny, nz = lattice
     src = GaussianPulse(12.5, 2.5).with_amplitudes((0.0, 0.0, 50.0), (0.0, 0.0, 0.0))
     sources = [((nx // 2, ny // 2, nz // 2), src)]
-    probes = [(nx // 2 + 16 * (k + 1), ny // 2, nz // 2) for k in range(4)] + [(nx // 2, ny // 2 + 16 * (k + 1), nz // 2) for k in range(4)]
+    probes = [(min(nx // 2 + 16 * (k + 1), nx - 1), ny // 2, nz // 2) for k in range(4)] + [(nx // 2, min(ny // 2 + 16 * (k + 1), ny - 1), nz // 2) for k in range(4)]
     w = configs.Workload(f"heterogeneous{nx}x{ny}x{nz}", tuple(lattice), configs.REDUCED_RES, configs.PhysicalConstants.REDUCED,
                          pal, ids, sources, probes, 0)
     return w

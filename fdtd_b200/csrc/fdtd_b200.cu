@@ -63,6 +63,7 @@ struct fdtd_b200_solver {
     bool fused = false;
     FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
     bool fused_maps_ready = false;
+    int n_sm = 0;                   // SMs of the device (queried at the first fused launch)
     int sm_smem_bytes = 0, sm_smem_reserved = 0;   // shared memory per SM / reserved per CTA (queried at the first fused launch)
     int cur_set = 0;                // which buffer set f[] currently points at
     void* mat = nullptr;
@@ -472,6 +473,29 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
     return FDTD_B200_OK;
 }
 
+// Planes per CTA march of the fused kernel.  A march of zc planes costs zc + c plane-times (c ≈ 2.5: the extra old-E plane, the
+// ring fill and the recomputed H' plane above the chunk), the CTAs run in waves of 2 per SM, and the last wave leaves the GPU
+// partly idle for ≈ 0.43 of a march: cost(zc) = (ceil(tiles · chunks / slots) + 0.43) · (zc + c) with balanced chunks.
+// c and 0.43 are fitted to tools/exp_zc_midsize.sh (profiles/r01_exp_zc_midsize.txt: 256³ best at 16 planes, 384³ at 24,
+// 512³ at 32..64, 128 slower than the model says); the previous rule (halve 64 until 3 waves exist) left 384³ at 64 planes, 10 % slower.
+int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes) {
+    if (h->n_sm == 0) {
+        if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
+    }
+    const double slots = 2.0 * h->n_sm;
+    static const int cand[] = {1, 2, 4, 6, 8, 12, 16, 20, 24, 28, 32, 40, 48, 56, 64};   // longer marches measured slower (128 planes: -6 %, profiles/r01_exp_plane_shape.txt)
+    int best = std::max(1, std::min(planes, 64));
+    double best_cost = 1e300;
+    for (int zc : cand) {
+        if (zc > planes && zc != cand[0]) { if (best_cost < 1e300) break; }
+        const int chunks = (planes + zc - 1) / zc;
+        const int zce = (planes + chunks - 1) / chunks;   // balanced
+        const double cost = (std::ceil(static_cast<double>(tiles) * chunks / slots) + 0.43) * (zce + 2.5);
+        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = zce; }
+    }
+    return best;
+}
+
 template <int EXACT, typename IdxT>
 int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) {
     constexpr int BX = 32, BY = 8;
@@ -523,8 +547,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     int zc = h->tune.zc;
     if (zc <= 0) {
         const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS);
-        zc = 64;
-        while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
+        zc = pick_fused_zc(h, tiles, z_hi - z_lo);
     }
     FusedPmlView Q{};
     if (pml) {
