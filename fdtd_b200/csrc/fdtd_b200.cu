@@ -88,6 +88,8 @@ struct fdtd_b200_solver {
     int pin_src_next = 0;
     float* pin_probe = nullptr;              // [PIN_SLOTS][n_probes_total * 6]
     uint64_t pin_probe_tick[PIN_SLOTS] = {}; // tick + 1 of the row a slot mirrors (0: none)
+    cudaEvent_t pin_probe_ev[PIN_SLOTS] = {}; // recorded behind the slot's copy: reading a mirrored row waits for this event only,
+                                              // so the caller can read step s while step s + 1 is already running
     size_t pin_probe_floats = 0;
 
     // probes
@@ -859,8 +861,10 @@ int probe_mirror_row(fdtd_b200_handle h, uint64_t tick) {
         probe_mirror_invalidate(h);
     }
     const int slot = static_cast<int>(tick % fdtd_b200_solver::PIN_SLOTS);
+    if (!h->pin_probe_ev[slot]) CU_TRY(h, cudaEventCreateWithFlags(&h->pin_probe_ev[slot], cudaEventDisableTiming));
     CU_TRY(h, cudaMemcpyAsync(h->pin_probe + slot * h->pin_probe_floats, h->d_probe_ring + (tick % h->ring_steps) * row, row * sizeof(float),
                               cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(h, cudaEventRecord(h->pin_probe_ev[slot], h->stream));
     h->pin_probe_tick[slot] = tick + 1;
     return FDTD_B200_OK;
 }
@@ -1156,6 +1160,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->pin_src) cudaFreeHost(h->pin_src);
     if (h->pin_probe) cudaFreeHost(h->pin_probe);
     for (auto& ev : h->pin_src_ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : h->pin_probe_ev) if (ev) cudaEventDestroy(ev);
     if (h->d_stage) cudaFree(h->d_stage);
     for (int a = 0; a < 3; ++a) pml_free_axis(h, a);
     if (h->psi_ghost) cudaFree(h->psi_ghost);
@@ -1777,12 +1782,15 @@ int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_st
     if (first_tick < h->probe_first_tick || first_tick + n_steps > h->tick) return fail(h, FDTD_B200_EINVAL, "probe range not sampled (yet)");
     if (h->tick - first_tick > h->ring_steps) return fail(h, FDTD_B200_EINVAL, "probe range already overwritten in the ring");
     if (int rc = set_device(h)) return rc;
-    CU_TRY(h, cudaStreamSynchronize(h->stream));
     const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
-    if (n_steps == 1 && h->pin_probe && h->pin_probe_tick[first_tick % fdtd_b200_solver::PIN_SLOTS] == first_tick + 1) {
-        std::memcpy(out, h->pin_probe + (first_tick % fdtd_b200_solver::PIN_SLOTS) * h->pin_probe_floats, row * sizeof(float));
+    const int pslot = static_cast<int>(first_tick % fdtd_b200_solver::PIN_SLOTS);
+    if (n_steps == 1 && h->pin_probe && h->pin_probe_ev[pslot] && h->pin_probe_tick[pslot] == first_tick + 1) {
+        // the row was mirrored into pinned memory behind its step: wait for that copy alone — later steps may be in flight
+        CU_TRY(h, cudaEventSynchronize(h->pin_probe_ev[pslot]));
+        std::memcpy(out, h->pin_probe + pslot * h->pin_probe_floats, row * sizeof(float));
         return FDTD_B200_OK;
     }
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
     uint64_t done = 0;
     while (done < n_steps) {
         const uint64_t r = (first_tick + done) % h->ring_steps;
@@ -2281,6 +2289,7 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
         end_step(h);
     }
     CU_TRY(h, cudaStreamWaitEvent(S, h->ev_push, 0));               // sync()/timer on the main stream cover the last pushes too
+    if (n_steps == 1 && h->n_probes_total) return probe_mirror_row(h, h->tick - 1);   // one-step protocol, as fdtd_b200_step
     return FDTD_B200_OK;
 }
 

@@ -461,3 +461,28 @@ def test_per_step_protocol_equals_the_batched_run(b200, fused):
         assert np.array_equal(st.read_probes(st.tick() - 1, 1), ref.read_probes(ref.tick() - 1, 1))
     assert st.tick() == ref.tick() == n + 4
     assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.read_field(b200.FieldComponent.E))
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_probe_rows_read_one_step_behind_equal_the_batched_run(b200, fused):
+    """The row of step s read while step s + 1 is already enqueued (fdtd_b200_read_probes waits for the event behind that row's
+    pinned copy, not for the stream) == the batched series; rows older than the pinned ring come from the device ring."""
+    w = _random_workload(b200, (128, 16, 12), seed=6)
+    probes = [(64, 8, 6), (0, 0, 0), (127, 15, 11)]
+    n = 30
+    _, _, ref_series = b200_run(b200, w, n, exact=True, probes=probes, fused=fused)
+    inst, st = b200_state(b200, w, exact=True, fused=fused)
+    st.register_probes(probes)
+    table = w.source_table(n)
+    pts = w.source_points()
+    rows = []
+    for s in range(n):
+        up = inst.begin_update(st)
+        for k, p in enumerate(pts):
+            up.set_forcing(p, b200.SourceValues(tuple(table[s, k, :3]), tuple(table[s, k, 3:])))
+        up.finish()
+        if s:
+            rows.append(st.read_probes(s - 1, 1)[0])
+    rows.append(st.read_probes(n - 1, 1)[0])
+    assert np.array_equal(np.stack(rows), ref_series)
+    assert np.array_equal(st.read_probes(n - 12, 1)[0], ref_series[n - 12])     # its pinned slot has been reused since
