@@ -19,7 +19,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib as L
-from .solver import DomainDescription, Material, Resolution
+from .solver import DomainDescription, GradedPml, Material, PhysicalConstants, PmlCoefficients, PmlProfiles, Resolution
 
 BALL, CUBOID, CYLINDER = 0, 1, 2
 
@@ -58,6 +58,52 @@ class Shape:
     def world_to_local_rotation(self) -> np.ndarray:
         """Row-major f32 3×3: the inverse (transpose) of the entity's rotation."""
         return np.ascontiguousarray(quaternion_to_matrix(self.rotation).T, dtype=np.float32)
+
+
+@dataclass(frozen=True)
+class PmlRegion:
+    """An entity carrying a `GradedPml` component and a cuboid collider (the only shape the application gives one,
+    cem-app/src/composer/presets.rs:119-143).  `pml(point)` of the reference (solver/runner.rs:633-675) finds the entities whose
+    AABB contains the point, casts a ray from the point along `pml.normal` against the collider (non-solid, at most the AABB's
+    diagonal far) and feeds the time of impact — the distance to the face the normal points at — as `depth` into
+    `PmlCoefficients::new_graded` together with −normal.  parry3d's f32 ray/cuboid routine is third-party (parry3d 0.25,
+    un-vendored): restated here as the slab method in f32 — parity unpinned."""
+    half_extents: tuple
+    pml: GradedPml
+    translation: tuple = (0.0, 0.0, 0.0)
+    rotation: tuple = (1.0, 0.0, 0.0, 0.0)
+
+    def aabb(self) -> tuple:
+        r = np.abs(quaternion_to_matrix(self.rotation)).astype(np.float32)
+        e = r @ np.asarray(self.half_extents, dtype=np.float32)
+        c = np.asarray(self.translation, dtype=np.float32)
+        return c - e, c + e
+
+    def cast_ray(self, origin: np.ndarray, direction: np.ndarray, max_toi: float) -> Optional[float]:
+        """Time of impact of origin + t·direction with the cuboid's surface (solid = false: a ray that starts inside hits
+        the face it leaves through), None beyond max_toi or on a miss."""
+        rot = quaternion_to_matrix(self.rotation).T.astype(np.float32)
+        o = rot @ (np.asarray(origin, dtype=np.float32) - np.asarray(self.translation, dtype=np.float32))
+        d = rot @ np.asarray(direction, dtype=np.float32)
+        h = np.asarray(self.half_extents, dtype=np.float32)
+        tmin, tmax = np.float32(0.0), np.float32(max_toi)
+        inside = bool(np.all(np.abs(o) <= h))
+        t_exit = np.float32(np.inf)
+        for a in range(3):
+            if d[a] == 0.0:
+                if abs(o[a]) > h[a]:
+                    return None
+                continue
+            inv = np.float32(1.0) / d[a]
+            t0, t1 = (-h[a] - o[a]) * inv, (h[a] - o[a]) * inv
+            if t0 > t1:
+                t0, t1 = t1, t0
+            tmin = max(tmin, t0)
+            t_exit = min(t_exit, t1)
+            if tmin > min(t_exit, tmax):
+                return None
+        toi = t_exit if inside else tmin
+        return float(toi) if np.isfinite(toi) and 0.0 <= toi <= max_toi else None
 
 
 @dataclass
@@ -101,6 +147,10 @@ class SceneDomain(DomainDescription):
     default_material: Material = Material.VACUUM
     palette: list = field(default_factory=list)     # filled by __post_init__: [default] + distinct shape materials (list order)
     labels: list = field(default_factory=list)
+    # entities with a GradedPml component (runner.rs:594-604); need the solver's resolution and constants for the coefficients
+    pml_regions: list = field(default_factory=list)
+    resolution: Optional[Resolution] = None
+    physical_constants: Optional[PhysicalConstants] = None
 
     def __post_init__(self):
         self.palette, self.labels = [self.default_material], []
@@ -131,6 +181,57 @@ class SceneDomain(DomainDescription):
         L.check(L.lib().fdtd_b200_rasterize_scene(device, dims, z_begin, z_end, self.c_transform(), self.c_shapes(), len(self.shapes), 0,
                                                   out.ctypes.data_as(C.POINTER(C.c_uint32))))
         return out
+
+    def pml(self, point) -> Optional[PmlCoefficients]:
+        """`DomainDescription::pml` as the application answers it (runner.rs:633-675): the first PML entity whose AABB holds the
+        point and whose collider the ray along its normal hits supplies graded coefficients (no merging: runner.rs:672)."""
+        if not self.pml_regions:
+            return None
+        if self.resolution is None or self.physical_constants is None:
+            raise ValueError("SceneDomain with PML regions needs resolution and physical_constants")
+        p = self.transformations.transform_point_from_solver_to_world(point)
+        for reg in self.pml_regions:
+            lo, hi = reg.aabb()
+            if np.any(p < lo) or np.any(p > hi):
+                continue
+            normal = np.asarray(reg.pml.normal, dtype=np.float32)
+            toi = reg.cast_ray(p, normal, float(np.linalg.norm((hi - lo).astype(np.float32))))
+            if toi is None:
+                continue
+            g = reg.pml
+            return PmlCoefficients.new_graded(self.resolution, self.physical_constants, g.m, g.m_a, g.sigma_max, g.kappa_max, g.a_max,
+                                              toi, tuple(-float(v) for v in normal.astype(np.float64)))
+        return None
+
+    @property
+    def pml_profiles(self) -> Optional[PmlProfiles]:
+        """The separable per-axis form the device runs (fdtd_b200_set_pml), without a per-cell sweep: every region must be a
+        slab of the lattice — normal along a lattice axis, covering the lattice's whole cross-section — so that its answer
+        depends on the coordinate along the normal only; the profile is `pml(point)` sampled along the lattice's centre lines.
+        Anything else raises (as `PmlProfiles.from_cells` does for a non-separable cell set)."""
+        if not self.pml_regions:
+            return None
+        n = self.transformations.lattice_size
+        centre = [v // 2 for v in n]
+        corners = [(x, y, z) for x in (0, n[0] - 1) for y in (0, n[1] - 1) for z in (0, n[2] - 1)]
+        cells = {}
+        for a in range(3):
+            for i in range(n[a]):
+                pt = list(centre)
+                pt[a] = i
+                co = self.pml(pt)
+                if co is None:
+                    continue
+                cells[tuple(pt)] = co
+                # separability: the same coordinate along a must answer the same at the far corners of the cross-section
+                for cpt in corners:
+                    q = list(cpt)
+                    q[a] = i
+                    cq = self.pml(q)
+                    if cq is None or not np.allclose(cq.c, co.c, rtol=1e-5, atol=0.0) or not np.allclose(cq.b, co.b, rtol=1e-5, atol=0.0):
+                        raise ValueError(f"PML region is not a slab of the lattice: axis {a} coordinate {i} answers differently at {tuple(q)} "
+                                         f"and {tuple(pt)} (the device runs separable per-axis profiles)")
+        return PmlProfiles.from_cells(n, cells) if cells else None
 
     # DomainDescription (lib.rs:47-68) — kept so the scene also works with a per-cell backend; not used on the B200 path
     def material(self, point) -> Material:

@@ -136,3 +136,67 @@ def test_oracle_without_pml_cells_is_the_reference_update(oracle):
         s.run(7)
         runs.append((s.field(oracle.E).copy(), s.field(oracle.H).copy()))
     assert np.array_equal(runs[0][0], runs[1][0]) and np.array_equal(runs[0][1], runs[1][1])
+
+
+def _pml_scene(b200, n=(24, 6, 5), rotation=(1.0, 0.0, 0.0, 0.0), half=(0.04, 0.5, 0.5), centre=(-0.08, 0.03, 0.02)):
+    from fdtd_b200.scene import CoordinateTransformations, PmlRegion, SceneDomain
+
+    res = b200.Resolution((0.01, 0.01, 0.01), 5e-4)
+    tf = CoordinateTransformations.for_fdtd(res, n, aabb_mins=(-0.12, 0.0, 0.0))
+    g = b200.GradedPml(4.0, 3.0, 2.5, 2.5, 0.1, (1.0, 0.0, 0.0))
+    reg = PmlRegion(half, g, centre, rotation)
+    return SceneDomain([], tf, pml_regions=[reg], resolution=res, physical_constants=b200.PhysicalConstants.REDUCED), reg, res, g
+
+
+def test_scene_pml_callback_casts_the_ray_along_the_normal(b200):
+    """`pml(point)` as the application answers it (runner.rs:633-675): depth = distance from the point to the collider face the
+    normal points at, coefficients from new_graded(depth, −normal); None outside the collider."""
+    sc, reg, res, g = _pml_scene(b200)
+    face = -0.08 + 0.04                                     # the +x face of the cuboid, world x
+    for x in range(24):
+        wx = np.float32(-0.12) + np.float32(0.01 * x)       # solver → world (f64 product, cast to f32)
+        co = sc.pml((x, 3, 2))
+        if wx > face + 1e-6:
+            assert co is None
+            continue
+        assert co is not None
+        depth = float(np.float32(face) - np.float32(np.float64(-0.12) + 0.01 * x))
+        want = b200.PmlCoefficients.new_graded(res, b200.PhysicalConstants.REDUCED, g.m, g.m_a, g.sigma_max, g.kappa_max, g.a_max, depth, (-1.0, 0.0, 0.0))
+        assert np.allclose(co.b, want.b, rtol=1e-4) and np.allclose(co.c, want.c, rtol=1e-3, atol=1e-30)
+        assert co.b[1] == 0 and co.b[2] == 0 and co.c[1] == 0 and co.c[2] == 0
+    # a ray that starts outside the (rotated) collider but inside its AABB hits the near face, a parallel miss gives None
+    assert reg.cast_ray(np.array([-0.2, 0.03, 0.02], np.float32), np.array([1, 0, 0], np.float32), 1.0) == pytest.approx(0.08, rel=1e-5)
+    assert reg.cast_ray(np.array([-0.2, 0.9, 0.02], np.float32), np.array([1, 0, 0], np.float32), 1.0) is None
+    assert reg.cast_ray(np.array([-0.2, 0.03, 0.02], np.float32), np.array([1, 0, 0], np.float32), 0.05) is None
+
+
+def test_scene_pml_profiles_equal_the_per_cell_sweep(b200):
+    sc, _, _, _ = _pml_scene(b200)
+    n = sc.transformations.lattice_size
+    cells = {}
+    for z in range(n[2]):
+        for y in range(n[1]):
+            for x in range(n[0]):
+                co = sc.pml((x, y, z))
+                if co is not None:
+                    cells[(x, y, z)] = co
+    brute = b200.PmlProfiles.from_cells(n, cells)
+    fast = sc.pml_profiles
+    assert fast.axes[1] is None and fast.axes[2] is None and brute.axes[1] is None
+    for k in range(4):
+        assert np.allclose(fast.axes[0][k], brute.axes[0][k], rtol=1e-6, atol=0.0)
+    assert np.count_nonzero(fast.axes[0][1]) >= 8
+    # the backend picks the profiles up from the scene (create_instance does not touch the GPU)
+    cfg = b200.FdtdSolverConfig.from_lattice(n, b200.Resolution((0.01, 0.01, 0.01), 5e-4), b200.PhysicalConstants.REDUCED)
+    inst = b200.FdtdB200Backend().create_instance(cfg, sc)
+    assert inst.pml is not None and inst.pml.any()
+
+
+def test_scene_pml_region_that_is_not_a_slab_is_refused(b200):
+    s = math.sin(math.pi / 8)
+    sc, _, _, _ = _pml_scene(b200, rotation=(math.cos(math.pi / 8), 0.0, s, 0.0))      # turned 45° about y
+    with pytest.raises(ValueError):
+        sc.pml_profiles
+    sc, _, _, _ = _pml_scene(b200, half=(0.04, 0.02, 0.5))                                # does not span the lattice in y
+    with pytest.raises(ValueError):
+        sc.pml_profiles
