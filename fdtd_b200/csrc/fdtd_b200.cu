@@ -96,6 +96,18 @@ struct fdtd_b200_solver {
     long long* d_probe_cells = nullptr;
     int* d_probe_slot = nullptr;
     float* d_probe_ring = nullptr;  // [ring_steps][n_probes_total][6]
+    // One-step calls (fdtd_b200_step(h, 1), fdtd_b200_p2p_step(h, 1): the reference's per-step protocol) write their probe row
+    // into a second ring in mapped pinned HOST memory (rings of at most 64 MB; hd_probe_ring = its device alias): the kernels
+    // store the few values straight over PCIe, a read is an event wait + a host memcpy, and no device→host copy sits between
+    // two steps.  Batched steps keep writing the HBM ring (the posted PCIe stores cost ≈ 3 µs per step, measured).
+    // row_in_host[r] says which ring holds row r.  FDTD_B200_STAGED_IO=1 disables the host ring.
+    float* h_probe_ring = nullptr;
+    float* hd_probe_ring = nullptr;
+    bool probe_rows_to_host = false;   // set for the duration of a one-step call
+    std::vector<unsigned char> row_in_host;
+    // one-step forcing: the kernels read the step's values straight from the pinned slot (device alias), no host→device copy
+    const float* src_vals_mapped = nullptr;
+    int pin_src_inflight = -1;      // slot whose event end_step records behind the step that consumes it
     uint32_t n_probes_total = 0, n_probes_local = 0;
     uint32_t ring_steps = 0;
     uint64_t probe_first_tick = 0;  // tick at registration
@@ -235,7 +247,7 @@ ForcingView forcing_view(fdtd_b200_handle h) {
     if (h->n_src && h->src_row < h->src_rows) {
         F.n = static_cast<int>(h->n_src);
         F.cells = h->d_src_cells;
-        F.vals = h->d_src_vals + h->src_row * static_cast<uint64_t>(h->n_src) * 6;
+        F.vals = h->src_vals_mapped ? h->src_vals_mapped : h->d_src_vals + h->src_row * static_cast<uint64_t>(h->n_src) * 6;
     }
     return F;
 }
@@ -246,7 +258,8 @@ ProbeView probe_view(fdtd_b200_handle h) {
         P.n = static_cast<int>(h->n_probes_local);
         P.cells = h->d_probe_cells;
         P.slot = h->d_probe_slot;
-        P.row = h->d_probe_ring + (h->tick % h->ring_steps) * static_cast<uint64_t>(h->n_probes_total) * 6;
+        P.row = ((h->probe_rows_to_host && h->hd_probe_ring) ? h->hd_probe_ring : h->d_probe_ring) +
+                (h->tick % h->ring_steps) * static_cast<uint64_t>(h->n_probes_total) * 6;
     }
     return P;
 }
@@ -854,6 +867,13 @@ void probe_mirror_invalidate(fdtd_b200_handle h) {
 int probe_mirror_row(fdtd_b200_handle h, uint64_t tick) {
     const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
     if (row == 0 || !h->d_probe_ring) return FDTD_B200_OK;
+    if (h->h_probe_ring && h->row_in_host[tick % h->ring_steps]) {   // the kernels wrote the row into host memory themselves: an event behind them is all it takes
+        const int slot = static_cast<int>(tick % fdtd_b200_solver::PIN_SLOTS);
+        if (!h->pin_probe_ev[slot]) CU_TRY(h, cudaEventCreateWithFlags(&h->pin_probe_ev[slot], cudaEventDisableTiming));
+        CU_TRY(h, cudaEventRecord(h->pin_probe_ev[slot], h->stream));
+        h->pin_probe_tick[slot] = tick + 1;
+        return FDTD_B200_OK;
+    }
     if (h->pin_probe_floats < row) {
         if (h->pin_probe) { CU_TRY(h, cudaStreamSynchronize(h->stream)); cudaFreeHost(h->pin_probe); h->pin_probe = nullptr; h->pin_probe_floats = 0; }
         CU_TRY(h, cudaMallocHost(&h->pin_probe, sizeof(float) * row * fdtd_b200_solver::PIN_SLOTS));
@@ -869,12 +889,29 @@ int probe_mirror_row(fdtd_b200_handle h, uint64_t tick) {
     return FDTD_B200_OK;
 }
 
+// one-step calls route their probe row into the host ring (fdtd_b200_solver::h_probe_ring) for the duration of the call
+struct HostRowScope {
+    fdtd_b200_handle h;
+    HostRowScope(fdtd_b200_handle h_, bool on) : h(h_) { h->probe_rows_to_host = on; }
+    ~HostRowScope() { h->probe_rows_to_host = false; }
+};
+
+bool staged_io() {
+    static const bool v = [] { const char* e = std::getenv("FDTD_B200_STAGED_IO"); return e && e[0] == '1'; }();
+    return v;
+}
+
 void end_step(fdtd_b200_handle h) {
+    if (h->pin_src_inflight >= 0) {   // the step that read the pinned forcing slot is enqueued: the slot is free behind it
+        if (cudaEventRecord(h->pin_src_ev[h->pin_src_inflight], h->stream) != cudaSuccess) (void)cudaGetLastError();
+        h->pin_src_inflight = -1;
+    }
+    if (h->n_probes_total && !h->row_in_host.empty()) h->row_in_host[h->tick % h->ring_steps] = (h->probe_rows_to_host && h->hd_probe_ring) ? 1 : 0;
     h->tick += 1;
     h->time += h->cfg.dt;  // accumulated (cpu/mod.rs:513), never tick*dt
     if (h->n_src) {
         h->src_row += 1;
-        if (h->src_row >= h->src_rows) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; }  // forcing is per step (cpu/mod.rs:370-377)
+        if (h->src_row >= h->src_rows) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; h->src_vals_mapped = nullptr; }  // forcing is per step (cpu/mod.rs:370-377)
     }
 }
 
@@ -1156,6 +1193,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->d_src_vals) cudaFree(h->d_src_vals);
     if (h->d_probe_cells) cudaFree(h->d_probe_cells);
     if (h->d_probe_slot) cudaFree(h->d_probe_slot);
+    if (h->h_probe_ring) cudaFreeHost(h->h_probe_ring);
     if (h->d_probe_ring) cudaFree(h->d_probe_ring);
     if (h->pin_src) cudaFreeHost(h->pin_src);
     if (h->pin_probe) cudaFreeHost(h->pin_probe);
@@ -1188,8 +1226,14 @@ int fdtd_b200_reset(fdtd_b200_handle h) {
     for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
     if (h->fused)
         for (int c = 0; c < 6; ++c) CU_TRY(h, cudaMemsetAsync(h->alt_alloc[c], 0, comp_floats * sizeof(float), h->stream));
+    if (h->h_probe_ring) {
+        CU_TRY(h, cudaStreamSynchronize(h->stream));
+        std::memset(h->h_probe_ring, 0, sizeof(float) * 6 * h->n_probes_total * static_cast<size_t>(h->ring_steps));
+    }
+    std::fill(h->row_in_host.begin(), h->row_in_host.end(), 0);
     if (h->d_probe_ring)
         CU_TRY(h, cudaMemsetAsync(h->d_probe_ring, 0, sizeof(float) * 6 * h->n_probes_total * static_cast<size_t>(h->ring_steps), h->stream));
+    h->src_vals_mapped = nullptr;
     for (int a = 0; a < 3; ++a)
         for (int fld = 0; fld < 2; ++fld)
             for (int g = 0; g < 2; ++g)
@@ -1498,7 +1542,7 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
             CU_TRY(h, cudaStreamSynchronize(h->stream));
             if (h->pin_src) { cudaFreeHost(h->pin_src); h->pin_src = nullptr; h->pin_src_floats = 0; }
             const size_t cap = std::max<size_t>(vals.size(), 96);
-            CU_TRY(h, cudaMallocHost(&h->pin_src, sizeof(float) * cap * fdtd_b200_solver::PIN_SLOTS));
+            CU_TRY(h, cudaHostAlloc(&h->pin_src, sizeof(float) * cap * fdtd_b200_solver::PIN_SLOTS, cudaHostAllocMapped | cudaHostAllocPortable));
             h->pin_src_floats = cap;
             for (auto& ev : h->pin_src_ev)
                 if (!ev) CU_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -1508,14 +1552,25 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
         CU_TRY(h, cudaEventSynchronize(h->pin_src_ev[slot]));   // a never-recorded event is complete
         float* p = h->pin_src + static_cast<size_t>(slot) * h->pin_src_floats;
         std::memcpy(p, vals.data(), sizeof(float) * vals.size());
-        CU_TRY(h, cudaMemcpyAsync(h->d_src_vals, p, sizeof(float) * vals.size(), cudaMemcpyHostToDevice, h->stream));
-        CU_TRY(h, cudaEventRecord(h->pin_src_ev[slot], h->stream));
+        void* dp = nullptr;
+        if (!staged_io() && cudaHostGetDevicePointer(&dp, p, 0) == cudaSuccess) {
+            // the step's kernels read the few values straight from the pinned slot; end_step records the slot's event behind them
+            h->src_vals_mapped = static_cast<const float*>(dp);
+            h->pin_src_inflight = slot;
+        } else {
+            (void)cudaGetLastError();
+            h->src_vals_mapped = nullptr;
+            CU_TRY(h, cudaMemcpyAsync(h->d_src_vals, p, sizeof(float) * vals.size(), cudaMemcpyHostToDevice, h->stream));
+            CU_TRY(h, cudaEventRecord(h->pin_src_ev[slot], h->stream));
+        }
         h->n_src = m;
         h->src_rows = 1;
         h->src_row = 0;
         return FDTD_B200_OK;
     }
     h->src_cells_host.clear();
+    h->src_vals_mapped = nullptr;
+    h->pin_src_inflight = -1;
     if (h->src_cells_cap < m) {
         if (h->d_src_cells) cudaFree(h->d_src_cells);
         h->d_src_cells = nullptr; h->src_cells_cap = 0;
@@ -1578,6 +1633,7 @@ int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
     if (int rc = set_device(h)) return rc;
     const int nzl = static_cast<int>(h->nzl);
+    const HostRowScope scope(h, n_steps == 1);
     for (uint64_t s = 0; s < n_steps; ++s) {
         if (h->fused) {
             if (int rc = launch_fused(h, 0, nzl)) return rc;
@@ -1743,6 +1799,8 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     if (h->d_probe_cells) { cudaFree(h->d_probe_cells); h->d_probe_cells = nullptr; }
     if (h->d_probe_slot) { cudaFree(h->d_probe_slot); h->d_probe_slot = nullptr; }
+    if (h->h_probe_ring) { cudaFreeHost(h->h_probe_ring); h->h_probe_ring = nullptr; h->hd_probe_ring = nullptr; }
+    h->row_in_host.clear();
     if (h->d_probe_ring) { cudaFree(h->d_probe_ring); h->d_probe_ring = nullptr; }
     h->n_probes_total = 0; h->n_probes_local = 0;
     h->probe_first_tick = h->tick;
@@ -1760,8 +1818,23 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
     std::sort(loc.begin(), loc.end());
     // the fused sampler writes one slot per distinct cell; duplicates are resolved on readback
     h->n_probes_total = n;
-    CU_TRY(h, cudaMalloc(&h->d_probe_ring, sizeof(float) * 6 * n * static_cast<size_t>(h->ring_steps)));
-    CU_TRY(h, cudaMemset(h->d_probe_ring, 0, sizeof(float) * 6 * n * static_cast<size_t>(h->ring_steps)));
+    const size_t ring_bytes = sizeof(float) * 6 * n * static_cast<size_t>(h->ring_steps);
+    if (ring_bytes <= (size_t(64) << 20) && !staged_io()) {
+        void* hp = nullptr;
+        void* dp = nullptr;
+        if (cudaHostAlloc(&hp, ring_bytes, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess &&
+            cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess) {
+            std::memset(hp, 0, ring_bytes);
+            h->h_probe_ring = static_cast<float*>(hp);
+            h->hd_probe_ring = static_cast<float*>(dp);
+        } else {
+            (void)cudaGetLastError();
+            if (hp) cudaFreeHost(hp);
+        }
+    }
+    h->row_in_host.assign(h->ring_steps, 0);
+    CU_TRY(h, cudaMalloc(&h->d_probe_ring, ring_bytes));
+    CU_TRY(h, cudaMemset(h->d_probe_ring, 0, ring_bytes));
     if (!loc.empty()) {
         std::vector<long long> lc(loc.size());
         std::vector<int> slot(loc.size());
@@ -1784,18 +1857,23 @@ int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_st
     if (int rc = set_device(h)) return rc;
     const size_t row = static_cast<size_t>(h->n_probes_total) * 6;
     const int pslot = static_cast<int>(first_tick % fdtd_b200_solver::PIN_SLOTS);
-    if (n_steps == 1 && h->pin_probe && h->pin_probe_ev[pslot] && h->pin_probe_tick[pslot] == first_tick + 1) {
-        // the row was mirrored into pinned memory behind its step: wait for that copy alone — later steps may be in flight
+    if (n_steps == 1 && (h->pin_probe || h->h_probe_ring) && h->pin_probe_ev[pslot] && h->pin_probe_tick[pslot] == first_tick + 1) {
+        // the row reached pinned memory behind its step: wait for that alone — later steps may be in flight
         CU_TRY(h, cudaEventSynchronize(h->pin_probe_ev[pslot]));
-        std::memcpy(out, h->pin_probe + pslot * h->pin_probe_floats, row * sizeof(float));
+        const bool in_host = h->h_probe_ring && h->row_in_host[first_tick % h->ring_steps];
+        const float* src = in_host ? h->h_probe_ring + (first_tick % h->ring_steps) * row : h->pin_probe + pslot * h->pin_probe_floats;
+        std::memcpy(out, src, row * sizeof(float));
         return FDTD_B200_OK;
     }
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     uint64_t done = 0;
     while (done < n_steps) {
         const uint64_t r = (first_tick + done) % h->ring_steps;
-        const uint64_t run = std::min<uint64_t>(n_steps - done, h->ring_steps - r);
-        CU_TRY(h, cudaMemcpy(out + done * row, h->d_probe_ring + r * row, run * row * sizeof(float), cudaMemcpyDeviceToHost));
+        uint64_t run = 1;   // the longest run of rows that live in the same ring
+        const bool in_host = h->h_probe_ring && h->row_in_host[r];
+        while (run < n_steps - done && r + run < h->ring_steps && (h->h_probe_ring && h->row_in_host[r + run]) == in_host) ++run;
+        if (in_host) std::memcpy(out + done * row, h->h_probe_ring + r * row, run * row * sizeof(float));
+        else CU_TRY(h, cudaMemcpy(out + done * row, h->d_probe_ring + r * row, run * row * sizeof(float), cudaMemcpyDeviceToHost));
         done += run;
     }
     return FDTD_B200_OK;
@@ -2252,6 +2330,7 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
     if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
     if (int rc = set_device(h)) return rc;
     const int n = static_cast<int>(h->nzl);
+    const HostRowScope scope(h, n_steps == 1);
     const bool split = n >= 3;                      // otherwise the whole slab is "boundary"
     const int lo = (split && h->lower.present) ? 1 : 0;
     const int hi = (split && h->upper.present) ? n - 1 : n;

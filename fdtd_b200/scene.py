@@ -151,6 +151,7 @@ class SceneDomain(DomainDescription):
     pml_regions: list = field(default_factory=list)
     resolution: Optional[Resolution] = None
     physical_constants: Optional[PhysicalConstants] = None
+    _pml_override: Optional[PmlProfiles] = field(default=None, repr=False)   # profiles assigned by the caller win over the regions
 
     def __post_init__(self):
         self.palette, self.labels = [self.default_material], []
@@ -209,8 +210,8 @@ class SceneDomain(DomainDescription):
         slab of the lattice — normal along a lattice axis, covering the lattice's whole cross-section — so that its answer
         depends on the coordinate along the normal only; the profile is `pml(point)` sampled along the lattice's centre lines.
         Anything else raises (as `PmlProfiles.from_cells` does for a non-separable cell set)."""
-        if not self.pml_regions:
-            return None
+        if self._pml_override is not None or not self.pml_regions:
+            return self._pml_override
         n = self.transformations.lattice_size
         centre = [v // 2 for v in n]
         corners = [(x, y, z) for x in (0, n[0] - 1) for y in (0, n[1] - 1) for z in (0, n[2] - 1)]
@@ -232,6 +233,10 @@ class SceneDomain(DomainDescription):
                         raise ValueError(f"PML region is not a slab of the lattice: axis {a} coordinate {i} answers differently at {tuple(q)} "
                                          f"and {tuple(pt)} (the device runs separable per-axis profiles)")
         return PmlProfiles.from_cells(n, cells) if cells else None
+
+    @pml_profiles.setter
+    def pml_profiles(self, profiles: Optional[PmlProfiles]) -> None:
+        self._pml_override = profiles
 
     # DomainDescription (lib.rs:47-68) — kept so the scene also works with a per-cell backend; not used on the B200 path
     def material(self, point) -> Material:
