@@ -486,3 +486,24 @@ def test_probe_rows_read_one_step_behind_equal_the_batched_run(b200, fused):
     rows.append(st.read_probes(n - 1, 1)[0])
     assert np.array_equal(np.stack(rows), ref_series)
     assert np.array_equal(st.read_probes(n - 12, 1)[0], ref_series[n - 12])     # its pinned slot has been reused since
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_one_step_and_batched_calls_share_one_probe_series(b200, fused):
+    """One-step calls write their probe row into the host-mapped ring, batched calls into the HBM ring: a read that spans both
+    kinds of rows, a reset in between and the FDTD_B200_STAGED_IO path all return the batched run's series."""
+    w = _random_workload(b200, (128, 16, 12), seed=8)
+    probes = [(64, 8, 6), (127, 15, 11), (1, 0, 3)]
+    n = 14
+    _, _, ref_series = b200_run(b200, w, n, exact=True, probes=probes, fused=fused)
+    inst, st = b200_state(b200, w, exact=True, fused=fused)
+    st.register_probes(probes)
+    for rnd in range(2):
+        st.set_source_table(w.source_points(), w.source_table(n))
+        for k in (1, 1, 1, 5, 1, 4, 1):
+            st.step(k)
+        assert st.tick() == n
+        assert np.array_equal(st.read_probes(0, n), ref_series)
+        assert np.array_equal(st.read_probes(2, 1)[0], ref_series[2]) and np.array_equal(st.read_probes(5, 3), ref_series[5:8])
+        st.reset()
+        st.register_probes(probes) if rnd == 0 else None
