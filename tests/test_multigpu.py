@@ -40,3 +40,16 @@ def test_two_ranks_with_cpml_inside_the_fused_kernel_over_peer_memory(b200):
            "--master-port", "29573", os.path.join(ROOT, "tools", "slab_parity.py"), "128,48,40", "25", "1", "1", "p2p", "6"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout and "pml=6" in res.stdout and "fused=True" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
+
+
+@pytest.mark.parametrize("lattice,fused,transport,pml", [("200,48,40", "1", "p2p", "0"), ("200,48,40", "1", "nccl", "0"), ("90,48,40", "0", "nccl", "0"),
+                                                       ("200,48,40", "1", "p2p", "6")])
+def test_two_ranks_with_padded_rows_bit_identical_to_one(b200, lattice, fused, transport, pml):
+    """Lattices whose nx is not a multiple of 16 (rows padded inside the library): halo planes, the pushed index
+    plane and the pushed ψ planes carry the pitch on both ranks."""
+    if b200.lib().fdtd_b200_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29574", os.path.join(ROOT, "tools", "slab_parity.py"), lattice, "25", "1", fused, transport, pml]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and "SLAB PARITY OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
