@@ -263,3 +263,20 @@ def test_scene_projection_checkpoint_and_errors_on_padded_rows(b200, tmp_path, m
     assert lib.fdtd_b200_register_probes(b._h, 1, cells.ctypes.data_as(C.POINTER(C.c_uint64))) == L.EINVAL
     cells[0] = n_cells - 1
     assert lib.fdtd_b200_register_probes(b._h, 1, cells.ctypes.data_as(C.POINTER(C.c_uint64))) == L.OK
+
+
+def test_a_full_coefficient_table_leaves_no_room_for_the_pad_row(b200, oracle):
+    """65 536 materials: the table has no free row for the pad cells, so the handle keeps the caller's nx (no padding) and runs the
+    one-thread-per-cell kernels — still bit-identical to the oracle."""
+    size = (70, 5, 4)
+    w, probes = _edge_workload(b200, size, seed=4)
+    rng = np.random.default_rng(3)
+    w.palette = [b200.Material(relative_permittivity=1.0 + 1e-4 * m) for m in range(65536)]
+    w.ids = rng.integers(0, 65536, w.n_cells).astype(np.uint32)
+    w.ids[0] = 0
+    init = random_fields(w, seed=5)
+    ref, s32 = oracle_run(oracle, w, 3, oracle.F32, init=init, probes=probes)
+    _, st, series = b200_run(b200, w, 3, exact=True, init=init, probes=probes, fused=True)
+    assert st.row_pitch == 70 and not st.uses_vec4 and st.index_bytes == 2
+    assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
+    assert np.array_equal(series, s32.astype(np.float32))
