@@ -241,7 +241,7 @@ def run_b200(args) -> None:
             dist.barrier()
 
     K, W = args.steps, args.warmup
-    table = w.source_table(W + 3 * K + 8)
+    table = w.source_table(W + 4 * K + 8)
     pts = w.source_points()
 
     # ---- device-resident throughput: forcing table already in HBM, no host traffic in the timed region ----
@@ -252,7 +252,10 @@ def run_b200(args) -> None:
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    st.set_profiling(True)
+    # Two passes of K steps.  The first is timed as a whole (one event pair around fdtd_b200_step(h, K)) and gives `value`; the
+    # second carries an event pair around every kernel launch and gives the dominant kernel's average duration for the
+    # roofline.  The per-launch events are kept out of the first pass because on several GPUs they sit between the boundary-
+    # and interior-stream launches of consecutive steps and cost 3 % (N=2: 249 against 256 Gcells/s; N=1: 0.2 %).
     launches0 = st.kernel_launches
     barrier()
     t0 = time.monotonic()
@@ -261,6 +264,12 @@ def run_b200(args) -> None:
     ms = st.timer_stop()
     barrier()
     launches = st.kernel_launches - launches0
+    st.set_profiling(True)
+    barrier()
+    st.timer_start()
+    advance(K)
+    ms_instrumented = st.timer_stop()
+    barrier()
     prof = [st.profile(0), st.profile(1)]
     st.set_profiling(False)
     if dist is not None:
@@ -365,7 +374,7 @@ def run_b200(args) -> None:
         traffic = None
     roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["achieved"] / peak,
                 "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
-                "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_cell"] * cells_total / n_gpus + psi_bytes / (1 if fused else 2), "kernel": dom["kernel"],
+                "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_cell"] * cells_total / n_gpus + psi_bytes / (1 if fused else 2), "kernel": dom["kernel"], "kernel_avg_from": f"a second pass of {K} steps with an event pair around every launch ({ms_instrumented / K:.4f} ms per step)",
                 "kernel_avg_ms": dom["avg_ms"], "peak_source": peak_src, "algorithmic_bytes_per_cell": dom["algorithmic_bytes_per_cell"],
                 # the same run against SURVEY §8d's two-pass figure (74 B per cell update): a fused pass can exceed 1.0 here
                 "step_equivalent_74B_gbs": BYTES_PER_CELL_STEP * value / n_gpus, "step_equivalent_74B_frac": BYTES_PER_CELL_STEP * value / n_gpus / peak,

@@ -553,6 +553,8 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     V.table_in_smem = ((pml && sizeof(IdxT) == 1) || h->n_table <= table_smem_max) ? 1 : 0;   // the PML instantiation assumes it for 8-bit indices (≤ 256 rows = 4 KB)
     V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nz = static_cast<int>(h->nzl);
     V.nxl = static_cast<int>(h->nxl);
+    static const bool late_issue = [] { const char* e = std::getenv("FDTD_B200_LATE_ISSUE"); return e && e[0] == '1'; }();
+    V.late_issue = late_issue ? 1 : 0;
     V.z_lo = z_lo; V.z_hi = z_hi;
     V.lo_open = h->z_begin > 0 ? 1 : 0;
     V.hi_open = h->z_end < h->nz ? 1 : 0;

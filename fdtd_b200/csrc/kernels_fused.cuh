@@ -67,6 +67,7 @@ struct FusedView {
     int nxl;              // lattice cells of a row (≤ nx; the rest are pad cells, kernels.cuh) — read by the XPAD instantiations
     int z_lo, z_hi;       // planes updated by this launch
     int lo_open, hi_open; // a neighbouring slab exists below / above: ghost planes -1 / nz hold its old fields
+    int late_issue;       // FDTD_B200_LATE_ISSUE=1: request the first planes after the forcing / probe scans (the A side of the A/B)
     float dx[3], inv_dx[3];
     // PUSH variant (boundary-plane launches of the peer-memory transport): the CTAs that own the slab's first / last plane
     // also store their results straight into the neighbouring GPUs' ghost planes over NVLink (peer-mapped pointers to the
@@ -232,7 +233,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    if (EARLY) first_issue();
+    if (EARLY && !V.late_issue) first_issue();
     if (V.table_in_smem) {
         for (int t = tid; t < V.n_table; t += NT) s_tab[t] = V.table[t];
     }
@@ -283,7 +284,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     bool has_src = false, has_probe = false;
     if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY, za, zb + 1, V.nx, sz_ll)) != 0;
     if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + LO::CORE_ROWS, za, zb, V.nx, sz_ll)) != 0;
-    if (!EARLY) first_issue();
+    if (!EARLY || V.late_issue) first_issue();
     if (n <= 0) return;
 
     const int tx = threadIdx.x, ty = threadIdx.y;
