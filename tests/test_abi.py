@@ -159,3 +159,26 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt and "fdtd_ref" not in txt, f
+
+
+def test_memory_required_counts_the_row_pitch(b200, monkeypatch):
+    """Lattices with nx >= 64 and nx % 16 != 0 are stored with padded rows (include/fdtd_b200.h, fdtd_b200_row_pitch):
+    150 -> 160, 100 -> 128 (the fused tile), 509 -> 512; below 64 cells, with the generic-kernel flag or with
+    FDTD_B200_NO_ROW_PADDING=1 the caller's nx is kept.  Host-side rule, no GPU needed."""
+    pc = b200.PhysicalConstants.REDUCED
+    res = b200.Resolution((1.0, 1.0, 1.0), 0.25)
+
+    def need(nx, **kw):
+        return b200.FdtdB200Backend(**kw).memory_required(b200.FdtdSolverConfig.from_lattice((nx, 10, 8), res, pc))
+
+    def expect(pitch, fused=False):
+        plane = pitch * 10
+        return (12 if fused else 6) * 4 * plane * 10 + plane * 9 + 16
+
+    assert need(150) == expect(160) and need(509) == expect(512) and need(100) == expect(128) and need(97) == expect(128)
+    assert need(96) == expect(96) and need(160) == expect(160) and need(63) == expect(63) and need(65) == expect(80)
+    assert need(150, fused_step=True) == expect(160, fused=True)          # pitch >= 128: two buffer sets
+    assert need(70, fused_step=True) == expect(80)                        # pitch < 128: the fused kernel is not eligible
+    assert need(150, force_generic_kernels=True) == expect(150)
+    monkeypatch.setenv("FDTD_B200_NO_ROW_PADDING", "1")
+    assert need(150) == expect(150)
