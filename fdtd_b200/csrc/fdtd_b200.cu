@@ -613,8 +613,8 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
 // ---- CPML passes ---------------------------------------------------------------------------------
 
 // Does the fused kernel's PML instantiation (kernels_fused.cuh) run the recursion, or the passes over the slabs?  In the
-// kernel: fused whole-lattice handles whose x slabs leave the column right of every 128-cell tile free (that recomputed
-// column carries no x-slab ψ) and put at most FusedPmlSmem::XS cells into one tile row.  FDTD_B200_PML_PASSES=1 forces
+// kernel: fused handles whose x slabs put at most FusedPmlSmem::XS cells into one 128-cell tile row (a slab may cross a tile
+// boundary: the recomputed column right of a tile then advances its own x-slab ψ_H from the current set).  FDTD_B200_PML_PASSES=1 forces
 // the passes (the two ways agree bit for bit: tests/test_pml_gpu.py).
 void pml_refresh_mode(fdtd_b200_handle h) {
     h->pml_in_kernel = false;
@@ -625,10 +625,8 @@ void pml_refresh_mode(fdtd_b200_handle h) {
         if (h->pml[a].ghost && !h->pml[a].d_map) return;
     }
     std::vector<int> per_tile(static_cast<size_t>(h->nx / 128 + 1), 0);
-    for (int x : h->pml[0].pos) {
-        if (x > 0 && x % 128 == 0) return;
+    for (int x : h->pml[0].pos)
         if (++per_tile[static_cast<size_t>(x / 128)] > 32) return;
-    }
     h->pml_in_kernel = true;
 }
 
@@ -1375,8 +1373,8 @@ int fdtd_b200_set_pml(fdtd_b200_handle h, int axis, const double* b_e, const dou
     pml_refresh_mode(h);
     if (h->fused && !h->pml_in_kernel && (h->z_begin != 0 || h->z_end != h->nz)) {
         pml_free_axis(h, axis);
-        return fail(h, FDTD_B200_ESTATE, "on a fused z-slab the PML must fit the fused kernel's tiling (no PML x-coordinate at a multiple of 128 other "
-                                         "than 0, at most 32 per 128-cell tile, FDTD_B200_PML_PASSES unset); use two-kernel handles otherwise");
+        return fail(h, FDTD_B200_ESTATE, "on a fused z-slab the PML must fit the fused kernel's tiling (at most 32 PML x-coordinates "
+                                         "per 128-cell tile, FDTD_B200_PML_PASSES unset); use two-kernel handles otherwise");
     }
     return FDTD_B200_OK;
 }

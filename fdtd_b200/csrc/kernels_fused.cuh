@@ -264,6 +264,13 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         }
     }
     __syncthreads();
+    // the recomputed column right of the tile (x0 + 128): its x-slab entry and (b, c), if a slab crosses the tile boundary there
+    int xr_k = -1;
+    float2 xr_bc = make_float2(0.f, 0.f);
+    if (PML && producer && Q.map[0] != nullptr && x0 + 4 * BX < V.nx) {
+        xr_k = __ldg(Q.map[0] + x0 + 4 * BX);
+        if (xr_k >= 0) xr_bc = __ldg(Q.bc_h[0] + xr_k);
+    }
     int nxs = 0;          // x-slab cells of a tile row (entries of the staging rows)
     int xjp = -1;         // entries of the own quad's four cells, one signed byte each
     if (PML) {
@@ -544,8 +551,17 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 float hy1 = leap<EXACT>(c.z, hy, c.w, -cy, my);
                 float hz1 = leap<EXACT>(c.z, hz, c.w, -cz, mz);
                 if (PML && gy < V.ny) {
-                    // the column right of the tile is never in an x slab (host-side eligibility); H'z takes the y slab's
-                    // G_yx (∂Ex/∂y), H'y the z slab's G_zx (∂Ex/∂z) — recomputed, the owner stores them
+                    // recomputed, the owner stores them: if the column right of the tile lies in an x slab (a slab that crosses
+                    // a tile boundary) its ψ_H is advanced from ∂Ey/∂x, ∂Ez/∂x (k_pml_axis<0, 0>: H_y += d_b·G_xz, H_z −= d_b·G_xy);
+                    // then H'z takes the y slab's G_yx (∂Ex/∂y), H'y the z slab's G_zx (∂Ex/∂z)
+                    if (xr_k >= 0) {
+                        const size_t qi = (static_cast<size_t>(zk) * V.ny + gy) * Q.n[0] + xr_k;
+                        const bool ghost = zk == V.nz;
+                        const float g0 = fmaf(xr_bc.x, (ghost ? Q.gh_ghost[0][0] : Q.gh_in[0][0])[qi], xr_bc.y * dey_dx);
+                        const float g1 = fmaf(xr_bc.x, (ghost ? Q.gh_ghost[0][1] : Q.gh_in[0][1])[qi], xr_bc.y * dez_dx);
+                        hy1 = fmaf(c.w, g1, hy1);
+                        hz1 = fmaf(-c.w, g0, hz1);
+                    }
                     const int ky = S.yk[r], kz = S.zk[k];
                     if (ky >= 0) {
                         const float2 bc = S.ybc[0][r];

@@ -188,8 +188,8 @@ int fdtd_b200_pml_coefficients(double dt, const fdtd_b200_physical_constants* co
 int fdtd_b200_pml_coefficients_graded(double dt, const fdtd_b200_physical_constants* constants, const fdtd_b200_graded_pml* g, double depth,
                                       const double normal[3], double b_out[3], double c_out[3]);
 /* Profiles of one axis (arrays of the global extent of that axis); b_e == NULL clears the axis.  ψ starts at zero.
- * Fused-step handles run the recursion inside the fused kernel when the x slabs fit its tiling (no PML coordinate at a
- * multiple of 128 other than 0, at most 32 per 128-cell tile; FDTD_B200_PML_PASSES=1 in the environment forces the
+ * Fused-step handles run the recursion inside the fused kernel when the x slabs fit its tiling (at most 32 PML
+ * x-coordinates per 128-cell tile; FDTD_B200_PML_PASSES=1 in the environment forces the
  * alternative), else — whole lattices only — as extra passes after it.  Fused z-slab handles need the in-kernel form (else
  * ESTATE: use two-kernel handles) and the peer-memory transport: a slab recomputes H' of the plane above it and receives
  * that plane's psi_H from the slab above with the boundary planes (fdtd_b200_p2p_*; set the PML on every slab BEFORE

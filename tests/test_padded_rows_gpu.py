@@ -116,7 +116,8 @@ def test_pml_on_padded_rows_equals_the_unpadded_handle(b200, monkeypatch, size, 
         assert np.array_equal(sk, su)
 
 
-@pytest.mark.parametrize("size,cuts,pml", [((200, 16, 24), (9,), 0), ((150, 10, 12), (1, 3, 10), 0), ((200, 16, 24), (3, 21), 5)])
+@pytest.mark.parametrize("size,cuts,pml", [((200, 16, 24), (9,), 0), ((150, 10, 12), (1, 3, 10), 0), ((200, 16, 24), (3, 21), 5),
+                                           ((130, 16, 24), (3, 21), 5)])   # x slab 125..129 crosses the tile boundary at 128: ghost ψ of the right column
 def test_fused_slabs_with_padded_rows_equal_one_domain(b200, size, cuts, pml):
     """z-slabs over the peer-memory transport (all handles in this process): halo planes, pushed index plane and pushed ψ_H carry
     the pitch on both sides; bit-identical to the whole-domain run, which is bit-identical to the oracle above."""

@@ -81,6 +81,8 @@ def test_fused_step_with_pml_equals_two_kernel_path(b200, exact):
 @pytest.mark.parametrize("size,thickness,exact,u16", [
     ((128, 18, 14), 4, True, False), ((256, 30, 20), 5, True, False), ((256, 30, 20), 9, False, False),
     ((384, 40, 70), 16, False, False), ((144, 23, 9), 3, True, True),
+    # x slabs that cross a 128-cell tile boundary (the recomputed column right of a tile lies in the slab): aligned and padded rows
+    ((272, 18, 14), 16, True, False), ((400, 12, 20), 20, False, False), ((520, 10, 9), 16, True, False), ((135, 9, 8), 9, True, False),
 ])
 def test_pml_inside_the_fused_kernel_equals_the_passes(b200, monkeypatch, size, thickness, exact, u16):
     """The fused kernel's PML instantiation (ψ_H ping-pong, ψ_E in place, x-slab ψ staged by cp.async) == the fused kernel
