@@ -7,11 +7,13 @@ import os
 
 from .build import LIB_PATH
 
+ABI_VERSION = 2
 OK, EINVAL, ENOMEM, ECUDA, ESTATE = 0, 1, 2, 3, 4
 FIELD_E, FIELD_H = 0, 1
 EXACT_ARITHMETIC = 1 << 0
 FORCE_GENERIC_KERNELS = 1 << 1
-FUSED_STEP = 1 << 2
+FUSED_STEP = 1 << 2        # ABI 1 name, ignored: the fused step is the default
+IN_PLACE_STEP = 1 << 3     # opt out of the fused step (two half-step kernels, fields updated in place)
 COLORMAP_CPU, COLORMAP_LINEAR, COLORMAP_APP_Z = 0, 1, 2
 (HALO_SEND_EX_TOP, HALO_SEND_EY_TOP, HALO_RECV_EX_LOW, HALO_RECV_EY_LOW,
  HALO_SEND_HX_BOTTOM, HALO_SEND_HY_BOTTOM, HALO_RECV_HX_HIGH, HALO_RECV_HY_HIGH,
@@ -73,6 +75,7 @@ SYMBOLS = {
     "fdtd_b200_index_materials": (C.c_int, [C.POINTER(Material), C.c_uint64, _u32p, C.POINTER(Material), C.c_uint32, _u32p]),
     "fdtd_b200_canonicalize_material_index": (C.c_int, [_u32p, C.c_uint64, C.POINTER(Material), C.c_uint32, _u32p, C.POINTER(Material), C.c_uint32, _u32p]),
     "fdtd_b200_memory_required": (C.c_size_t, [C.POINTER(Config), C.c_uint32]),
+    "fdtd_b200_choose_step_mode": (C.c_int, [C.POINTER(Config), C.c_uint32, C.c_uint64, _u32p, _u64p]),
     "fdtd_b200_create": (C.c_int, [C.POINTER(Config), C.POINTER(PhysicalConstants), C.POINTER(Material), C.c_uint32, _u32p, C.POINTER(_H)]),
     "fdtd_b200_create_from_table": (C.c_int, [C.POINTER(Config), C.POINTER(CoefficientsF32), C.c_uint32, _u32p, C.POINTER(_H)]),
     "fdtd_b200_destroy": (None, [_H]),
@@ -92,6 +95,8 @@ SYMBOLS = {
     "fdtd_b200_pml_state_floats": (C.c_uint64, [_H]),
     "fdtd_b200_read_pml_state": (C.c_int, [_H, _fp]),
     "fdtd_b200_write_pml_state": (C.c_int, [_H, _fp]),
+    "fdtd_b200_memory_in_use": (C.c_uint64, [_H]),
+    "fdtd_b200_step_path": (C.c_int, [_H, C.c_char_p, C.c_size_t]),
     "fdtd_b200_index_bytes": (C.c_int, [_H]),
     "fdtd_b200_uses_vec4": (C.c_int, [_H]),
     "fdtd_b200_uses_bulk": (C.c_int, [_H]),
@@ -153,7 +158,7 @@ def lib() -> C.CDLL:
         fn = getattr(l, name)  # AttributeError here = header/library mismatch
         fn.restype = res
         fn.argtypes = args
-    if l.fdtd_b200_abi_version() != 1:
+    if l.fdtd_b200_abi_version() != ABI_VERSION:
         raise ImportError("fdtd_b200 ABI version mismatch")
     _lib = l
     return l

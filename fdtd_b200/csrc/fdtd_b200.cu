@@ -9,6 +9,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -61,6 +63,7 @@ struct fdtd_b200_solver {
     float* alt_alloc[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // ping-pong set of the fused step
     float* g[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool fused = false;
+    std::string fused_why_not;      // why this handle is not on the fused step (empty when it is); fdtd_b200_step_path
     FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
     bool fused_maps_ready = false;
     int n_sm = 0;                   // SMs of the device (queried at the first fused launch)
@@ -82,6 +85,8 @@ struct fdtd_b200_solver {
     // the cell set is unchanged), and a one-step fdtd_b200_step mirrors its probe row into pinned host memory
     static constexpr int PIN_SLOTS = 8;
     std::vector<long long> src_cells_host;   // what d_src_cells holds
+    std::vector<uint64_t> src_cells_raw;     // the caller's cell list that produced it (per-step fast path: compared, not rebuilt)
+    std::vector<uint32_t> src_perm;          // column of the caller's list behind each device entry
     float* pin_src = nullptr;                // [PIN_SLOTS][pin_src_floats]
     size_t pin_src_floats = 0;
     cudaEvent_t pin_src_ev[PIN_SLOTS] = {};
@@ -158,7 +163,15 @@ struct fdtd_b200_solver {
         std::vector<void*> opened;          // cudaIpcOpenMemHandle results to close
         float* psi_ghost = nullptr;         // the neighbour's ψ_H receive buffer (lower neighbour only)
     } lower, upper;
-    unsigned long long* d_flags = nullptr;  // [0] pushes received from below, [1] from above, [2] flag-wait timeout marker
+    unsigned long long* d_flags = nullptr;  // [0] pushes received from below, [1] from above
+    // Sticky timeout marker of the flag waits, in mapped pinned HOST memory (hd_timeout = its device alias): a wait that gives
+    // up stores the push count it was waiting for; from then on every wait returns at once and every entry point that steps,
+    // reads or writes state fails with FDTD_B200_ECUDA (p2p_poisoned) — a lagging or dead neighbour never yields fields or
+    // probe rows computed on stale ghost planes.
+    volatile unsigned long long* h_timeout = nullptr;
+    unsigned long long* hd_timeout = nullptr;
+    bool halos_dirty = false;               // reset / set_time / write_field / write_pml_state since the last refresh: the neighbours'
+                                            // ghost planes (and psi receive slots) are stale, fdtd_b200_p2p_step refuses to run
     uint64_t halo_seq = 0;                  // pushes made to (and expected from) each neighbour so far
     bool p2p = false, p2p_mat_sent = false;
     cudaStream_t bstream = nullptr;         // high-priority stream of the boundary planes and the pushes
@@ -216,6 +229,23 @@ Tune parse_tune() {
         if (std::sscanf(s, "%d,%d,%d,%d,%d,%d,%d", &a, &b, &c, &d, &e, &f, &g) >= 1) { t.bx = a; t.by = b; t.zc = c; t.variant = d; t.stages = e; t.table_smem = f; t.l2_promotion = g; }
     }
     return t;
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per kernel and device, not once per launch (≈ 1 µs of host time, which
+// shows on lattices whose step is a few µs).  The limit is a property of the function in the device's context, shared by every
+// handle of the process, so it is only ever raised.
+template <typename K>
+int raise_smem_limit(fdtd_b200_handle h, K kernel, size_t smem) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, size_t> limit;
+    const std::pair<int, const void*> key(h->device, reinterpret_cast<const void*>(kernel));
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = limit.find(key);
+    if (it != limit.end() && it->second >= smem) return FDTD_B200_OK;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return -1; }
+    limit[key] = smem;
+    return FDTD_B200_OK;
 }
 
 int set_device(fdtd_b200_handle h) {
@@ -400,11 +430,11 @@ int launch_bulk(fdtd_b200_handle h, bool e_step, int z_lo, int z_hi) {
     if (e_step) {
         const ProbeView P = probe_view(h);
         auto k = k_update_e_bulk<EXACT, IdxT, BX, BY, S>;
-        CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
         k<<<grid, block, smem, h->stream>>>(L, F, P, z_lo, z_hi, zc);
     } else {
         auto k = k_update_h_bulk<EXACT, IdxT, BX, BY, S>;
-        CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
         k<<<grid, block, smem, h->stream>>>(L, F, z_lo, z_hi, zc);
     }
     h->launches += 1;
@@ -441,8 +471,16 @@ bool use_bulk(fdtd_b200_handle h) {
 
 
 // ---- fused single-pass step (kernels_fused.cuh) --------------------------------------------------------
-bool fused_eligible(uint64_t pitch, int idx_bytes, bool vec4) {
-    return vec4 && (pitch * idx_bytes) % 16 == 0 && pitch >= 128;
+// Step mode of a handle: the fused single-pass step unless the caller opted out or the lattice is not eligible.  Returns
+// an empty string for "fused", else the reason (reported by fdtd_b200_step_path; there are no silent fallbacks).
+std::string fused_refusal(uint32_t flags, int tune_variant, uint64_t pitch, int idx_bytes) {
+    if (flags & FDTD_B200_FORCE_GENERIC_KERNELS) return "FDTD_B200_FORCE_GENERIC_KERNELS";
+    if (flags & FDTD_B200_IN_PLACE_STEP) return "in-place step requested (FDTD_B200_IN_PLACE_STEP)";
+    if (tune_variant == 0 || tune_variant == 1) return "FDTD_B200_TUNE selects a two-kernel variant";
+    if (pitch % 4 != 0) return "row pitch " + std::to_string(pitch) + " is not a multiple of 4 cells";
+    if (pitch < 128) return "row pitch " + std::to_string(pitch) + " < 128 cells (one tile of the fused kernel)";
+    if ((pitch * idx_bytes) % 16 != 0) return "index rows are not 16-byte aligned";
+    return std::string();
 }
 
 // Row pitch of a lattice of nx cells per row (see fdtd_b200_solver::nxl).  Rows of at least 64 cells are padded to the next
@@ -603,7 +641,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
         if (h->upper.present)
             for (int c = 0; c < 2; ++c) V.push_up[c] = h->upper.field[pend][c];
     }
-    CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
     k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc, Q);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
@@ -915,6 +953,14 @@ void end_step(fdtd_b200_handle h) {
     }
 }
 
+// Sticky failure of the peer-memory transport (fdtd_b200_solver::h_timeout).  Cheap: one read of host memory.
+int p2p_poisoned(fdtd_b200_handle h) {
+    if (h->h_timeout && *h->h_timeout)
+        return fail(h, FDTD_B200_ECUDA, "timed out waiting for a neighbour's halo flag (push #" + std::to_string(*h->h_timeout) +
+                                            "): ranks out of step or a neighbour died; this handle's state is invalid (destroy it)");
+    return FDTD_B200_OK;
+}
+
 int ensure_stage(fdtd_b200_handle h, size_t floats) {
     if (h->stage_floats >= floats) return FDTD_B200_OK;
     if (h->d_stage) { cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_floats = 0; }
@@ -991,8 +1037,8 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
         CU_NEW(cudaMemsetAsync(h->alloc[c], 0, comp_floats * sizeof(float), h->stream));
         h->f[c] = h->alloc[c] + h->plane;
     }
-    h->fused = ((cfg->flags & FDTD_B200_FUSED_STEP) || h->tune.variant == 2) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
-               fused_eligible(h->nx, h->idx_bytes, h->vec4);
+    h->fused_why_not = fused_refusal(cfg->flags, h->tune.variant, h->nx, h->idx_bytes);
+    h->fused = h->fused_why_not.empty();
     if (h->fused) {
         for (int c = 0; c < 6; ++c) {
             CU_NEW(cudaMalloc(&h->alt_alloc[c], comp_floats * sizeof(float)));
@@ -1153,10 +1199,28 @@ size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_byt
     const uint64_t pitch = row_pitch(cfg->nx, cfg->flags, index_bytes == 1 ? 1 : 65535);
     const uint64_t plane = pitch * cfg->ny;
     // 6 fp32 components with two ghost planes each + the material index (cf. 136 B/cell cpu/mod.rs:217-221,
-    // 80 B/cell wgpu/mod.rs:129-133)
-    const bool fused = (cfg->flags & FDTD_B200_FUSED_STEP) && !(cfg->flags & FDTD_B200_FORCE_GENERIC_KERNELS) &&
-                       fused_eligible(pitch, static_cast<int>(index_bytes), pitch % 4 == 0);
+    // 80 B/cell wgpu/mod.rs:129-133); the fused step keeps two sets of the fields
+    const bool fused = fused_refusal(cfg->flags, parse_tune().variant, pitch, static_cast<int>(index_bytes)).empty();
     return static_cast<size_t>((fused ? 12 : 6) * sizeof(float) * plane * (nzl + 2) + plane * (nzl + 1) * index_bytes + 16);
+}
+
+int fdtd_b200_choose_step_mode(const fdtd_b200_config* cfg, uint32_t index_bytes, uint64_t memory_limit, uint32_t* flags_out,
+                               uint64_t* required_out) {
+    std::string why;
+    if (!validate_cfg(cfg, &why)) return fail(nullptr, FDTD_B200_EINVAL, why);
+    if (index_bytes != 1 && index_bytes != 2) return fail(nullptr, FDTD_B200_EINVAL, "index_bytes must be 1 or 2");
+    fdtd_b200_config c = *cfg;
+    c.flags &= ~static_cast<uint32_t>(FDTD_B200_IN_PLACE_STEP);
+    uint64_t need = fdtd_b200_memory_required(&c, index_bytes);
+    if (memory_limit && need > memory_limit) {
+        c.flags |= FDTD_B200_IN_PLACE_STEP;
+        need = fdtd_b200_memory_required(&c, index_bytes);
+    }
+    if (flags_out) *flags_out = c.flags;
+    if (required_out) *required_out = need;
+    if (memory_limit && need > memory_limit)
+        return fail(nullptr, FDTD_B200_ENOMEM, "lattice needs " + std::to_string(need) + " bytes of device memory, the limit is " + std::to_string(memory_limit));
+    return FDTD_B200_OK;
 }
 
 int fdtd_b200_create_from_table(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32* table, uint32_t n_table,
@@ -1205,6 +1269,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->bstream) cudaStreamSynchronize(h->bstream);
     for (auto* link : {&h->lower, &h->upper}) { for (void* p : link->opened) cudaIpcCloseMemHandle(p); link->opened.clear(); }
     if (h->d_flags) cudaFree(h->d_flags);
+    if (h->h_timeout) cudaFreeHost(const_cast<unsigned long long*>(h->h_timeout));
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     if (h->ev_bnd) cudaEventDestroy(h->ev_bnd);
     if (h->ev_push) cudaEventDestroy(h->ev_push);
@@ -1238,6 +1303,13 @@ int fdtd_b200_reset(fdtd_b200_handle h) {
         for (int fld = 0; fld < 2; ++fld)
             for (int g = 0; g < 2; ++g)
                 if (h->pml[a].psi[fld][g]) CU_TRY(h, cudaMemsetAsync(h->pml[a].psi[fld][g], 0, h->pml[a].floats * sizeof(float), h->stream));
+    for (int a = 0; a < 3; ++a)
+        for (int g = 0; g < 2; ++g)
+            if (h->pml[a].psi_alt[g]) CU_TRY(h, cudaMemsetAsync(h->pml[a].psi_alt[g], 0, h->pml[a].floats * sizeof(float), h->stream));
+    if (h->psi_ghost)   // the upper neighbour's psi_H receive slots (both tick parities)
+        CU_TRY(h, cudaMemsetAsync(h->psi_ghost, 0, std::max<size_t>(4 * (h->ghost_plane[0] + h->ghost_plane[1] + h->ghost_plane[2]), 1) * sizeof(float), h->stream));
+    h->halos_dirty = true;
+    h->pin_src_inflight = -1;
     h->n_src = 0; h->src_rows = 0; h->src_row = 0;
     h->tick = 0;
     h->time = 0.0;
@@ -1267,12 +1339,7 @@ int fdtd_b200_sync(fdtd_b200_handle h) {
     if (int rc = set_device(h)) return rc;
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     if (h->bstream) CU_TRY(h, cudaStreamSynchronize(h->bstream));
-    if (h->d_flags) {
-        unsigned long long marker = 0;
-        CU_TRY(h, cudaMemcpy(&marker, h->d_flags + 2, sizeof marker, cudaMemcpyDeviceToHost));
-        if (marker) return fail(h, FDTD_B200_ECUDA, "timed out waiting for a neighbour's halo flag (push #" + std::to_string(marker) + "): ranks out of step?");
-    }
-    return FDTD_B200_OK;
+    return p2p_poisoned(h);
 }
 
 int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time) {
@@ -1281,6 +1348,8 @@ int fdtd_b200_set_time(fdtd_b200_handle h, uint64_t tick, double time) {
     h->tick = tick;
     h->time = time;
     h->n_src = 0; h->src_rows = 0; h->src_row = 0;
+    h->src_vals_mapped = nullptr; h->pin_src_inflight = -1;
+    h->halos_dirty = true;   // tick parity selects the psi receive slot and the push destination
     h->probe_first_tick = tick;
     probe_mirror_invalidate(h);
     return FDTD_B200_OK;
@@ -1404,7 +1473,8 @@ static int pml_state_copy(fdtd_b200_handle h, float* host, bool to_host) {
                 off += A.floats;
             }
     CU_TRY(h, cudaStreamSynchronize(h->stream));
-    return FDTD_B200_OK;
+    if (!to_host) h->halos_dirty = true;   // the slab below holds psi_H of our first plane
+    return p2p_poisoned(h);
 }
 int fdtd_b200_read_pml_state(fdtd_b200_handle h, float* out) { return pml_state_copy(h, out, true); }
 int fdtd_b200_write_pml_state(fdtd_b200_handle h, const float* in) { return pml_state_copy(h, const_cast<float*>(in), false); }
@@ -1416,6 +1486,46 @@ uint64_t fdtd_b200_row_pitch(fdtd_b200_handle h) { return h ? h->nx : 0; }
 int fdtd_b200_uses_vec4(fdtd_b200_handle h) { return h && h->vec4 ? 1 : 0; }
 int fdtd_b200_uses_bulk(fdtd_b200_handle h) { return h && use_bulk(h) ? 1 : 0; }
 int fdtd_b200_uses_fused(fdtd_b200_handle h) { return h && h->fused ? 1 : 0; }
+
+uint64_t fdtd_b200_memory_in_use(fdtd_b200_handle h) {
+    if (!h) return 0;
+    const uint64_t comp = static_cast<uint64_t>(h->plane) * (h->nzl + 2) * sizeof(float);
+    uint64_t b = (h->fused ? 12 : 6) * comp + (h->n_local + h->plane) * h->idx_bytes + 16 + sizeof(float4) * h->n_table;
+    b += h->src_cells_cap * sizeof(long long) + h->src_vals_cap * sizeof(float) + h->stage_floats * sizeof(float);
+    if (h->d_probe_ring) b += sizeof(float) * 6 * h->n_probes_total * static_cast<uint64_t>(h->ring_steps) + h->n_probes_local * (sizeof(long long) + sizeof(int));
+    for (int a = 0; a < 3; ++a) {
+        const auto& A = h->pml[a];
+        if (!A.n) continue;
+        b += A.floats * sizeof(float) * (4 + (A.psi_alt[0] ? 2 : 0)) + static_cast<uint64_t>(A.n) * (sizeof(int) + 2 * sizeof(float2));
+    }
+    if (h->psi_ghost) b += 4 * (h->ghost_plane[0] + h->ghost_plane[1] + h->ghost_plane[2]) * sizeof(float);
+    if (h->d_flags) b += 64;
+    return b;
+}
+
+int fdtd_b200_step_path(fdtd_b200_handle h, char* buf, size_t cap) {
+    if (!h) return 0;
+    const int mode = arithmetic_mode(h);
+    const std::string arith = mode == 0 ? "fast" : (mode == 1 ? "exact" : "exact-div");
+    const std::string idx = h->idx_bytes == 1 ? "u8" : "u16";
+    std::string s;
+    if (h->fused) {
+        s = "fused: k_step_fused<" + arith + "," + idx + ">";
+        if (h->nx != h->nxl) s += " xpad";
+        if (h->has_pml) s += h->pml_in_kernel ? " + CPML inside the kernel" : " + CPML passes (x slabs do not fit the in-kernel tiling, or FDTD_B200_PML_PASSES=1)";
+        if (h->p2p) s += " + peer-memory halos";
+    } else {
+        s = std::string("two-kernel (") + (use_bulk(h) ? "bulk" : (h->vec4 ? "vec4" : "generic")) + "): k_update_{h,e}_" +
+            (use_bulk(h) ? "bulk" : (h->vec4 ? "vec4" : "generic")) + "<" + arith + "," + idx + ">; not fused: " + h->fused_why_not;
+        if (h->has_pml) s += " + CPML passes";
+    }
+    if (buf && cap) {
+        const size_t n = std::min(cap - 1, s.size());
+        std::memcpy(buf, s.data(), n);
+        buf[n] = 0;
+    }
+    return static_cast<int>(s.size());
+}
 uint64_t fdtd_b200_kernel_launches(fdtd_b200_handle h) { return h ? h->launches : 0; }
 
 int fdtd_b200_set_profiling(fdtd_b200_handle h, int enabled) {
@@ -1502,12 +1612,56 @@ int fdtd_b200_read_coefficient_table(fdtd_b200_handle h, fdtd_b200_coefficients_
 
 int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_t* cells, uint64_t n_steps, const float* values) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
-    if (n_src == 0 || n_steps == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; return FDTD_B200_OK; }
+    if (n_src == 0 || n_steps == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; h->src_vals_mapped = nullptr; h->pin_src_inflight = -1; return FDTD_B200_OK; }
     if (!cells || !values) return fail(h, FDTD_B200_EINVAL, "NULL cells/values");
     const uint64_t n_global = h->nxl * h->ny * h->nz;
     for (uint32_t k = 0; k < n_src; ++k)
         if (cells[k] >= n_global) return fail(h, FDTD_B200_EINVAL, "set_forcing called with invalid point (cell index outside the lattice)");
     if (int rc = set_device(h)) return rc;
+
+    // per-step fast path (the reference protocol: set_forcing* → finish every step, runner.rs:522-526): the same cell list as
+    // the last call → the sorted/deduplicated device table is still right and only the values move, straight into a pinned
+    // slot — no allocation, no hashing, no sort, no synchronisation.  The slot is read by the step's kernels through its device
+    // alias (or copied in stream order with FDTD_B200_STAGED_IO=1) and reused only after the event end_step records behind them.
+    if (n_steps == 1 && h->d_src_cells && !h->src_perm.empty() && h->src_cells_raw.size() == n_src &&
+        std::memcmp(h->src_cells_raw.data(), cells, sizeof(uint64_t) * n_src) == 0 && h->src_vals_cap >= h->src_perm.size() * 6) {
+        const uint32_t m = static_cast<uint32_t>(h->src_perm.size());
+        const size_t floats = static_cast<size_t>(m) * 6;
+        if (h->pin_src_floats < floats) {
+            CU_TRY(h, cudaStreamSynchronize(h->stream));
+            if (h->pin_src) { cudaFreeHost(h->pin_src); h->pin_src = nullptr; h->pin_src_floats = 0; }
+            const size_t cap = std::max<size_t>(floats, 96);
+            CU_TRY(h, cudaHostAlloc(&h->pin_src, sizeof(float) * cap * fdtd_b200_solver::PIN_SLOTS, cudaHostAllocMapped | cudaHostAllocPortable));
+            h->pin_src_floats = cap;
+            for (auto& ev : h->pin_src_ev)
+                if (!ev) CU_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        }
+        const int slot = h->pin_src_next;
+        h->pin_src_next = (slot + 1) % fdtd_b200_solver::PIN_SLOTS;
+        if (cudaEventQuery(h->pin_src_ev[slot]) != cudaSuccess) {   // a never-recorded event is complete
+            (void)cudaGetLastError();
+            CU_TRY(h, cudaEventSynchronize(h->pin_src_ev[slot]));
+        }
+        float* p = h->pin_src + static_cast<size_t>(slot) * h->pin_src_floats;
+        for (uint32_t q = 0; q < m; ++q) std::memcpy(p + 6 * q, values + 6 * static_cast<size_t>(h->src_perm[q]), 6 * sizeof(float));
+        void* dp = nullptr;
+        if (!staged_io() && cudaHostGetDevicePointer(&dp, p, 0) == cudaSuccess) {
+            // the step's kernels read the few values straight from the pinned slot; end_step records the slot's event behind them
+            h->src_vals_mapped = static_cast<const float*>(dp);
+            h->pin_src_inflight = slot;
+        } else {
+            (void)cudaGetLastError();
+            h->src_vals_mapped = nullptr;
+            CU_TRY(h, cudaMemcpyAsync(h->d_src_vals, p, sizeof(float) * floats, cudaMemcpyHostToDevice, h->stream));
+            CU_TRY(h, cudaEventRecord(h->pin_src_ev[slot], h->stream));
+        }
+        h->n_src = m;
+        h->src_rows = 1;
+        h->src_row = 0;
+        return FDTD_B200_OK;
+    }
+
+    const uint64_t* raw_cells = cells;
     std::vector<uint64_t> pitched;
     if (h->nx != h->nxl) {   // padded rows: the kernels look cells up by their index in the pitched arrays
         pitched.resize(n_src);
@@ -1525,7 +1679,9 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
     std::vector<std::pair<long long, uint32_t>> kept(last.begin(), last.end());
     std::sort(kept.begin(), kept.end());
     const uint32_t m = static_cast<uint32_t>(kept.size());
-    if (m == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; return FDTD_B200_OK; }
+    h->src_cells_raw.clear();
+    h->src_perm.clear();
+    if (m == 0) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; h->src_vals_mapped = nullptr; h->pin_src_inflight = -1; return FDTD_B200_OK; }
 
     std::vector<long long> lc(m);
     std::vector<float> vals(static_cast<size_t>(n_steps) * m * 6);
@@ -1534,40 +1690,6 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
         for (uint32_t q = 0; q < m; ++q)
             std::memcpy(&vals[(s * m + q) * 6], values + (s * n_src + kept[q].second) * 6, 6 * sizeof(float));
 
-    // per-step fast path: same cell set as the table on the device → only the values move, asynchronously.  The copy is
-    // ordered after every enqueued kernel that reads the old row (same stream; p2p_step joins its boundary stream back into
-    // it), and the pinned slot is reused only after its own copy has completed.
-    if (n_steps == 1 && h->d_src_cells && lc == h->src_cells_host && h->src_vals_cap >= vals.size()) {
-        if (h->pin_src_floats < vals.size()) {
-            CU_TRY(h, cudaStreamSynchronize(h->stream));
-            if (h->pin_src) { cudaFreeHost(h->pin_src); h->pin_src = nullptr; h->pin_src_floats = 0; }
-            const size_t cap = std::max<size_t>(vals.size(), 96);
-            CU_TRY(h, cudaHostAlloc(&h->pin_src, sizeof(float) * cap * fdtd_b200_solver::PIN_SLOTS, cudaHostAllocMapped | cudaHostAllocPortable));
-            h->pin_src_floats = cap;
-            for (auto& ev : h->pin_src_ev)
-                if (!ev) CU_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        }
-        const int slot = h->pin_src_next;
-        h->pin_src_next = (slot + 1) % fdtd_b200_solver::PIN_SLOTS;
-        CU_TRY(h, cudaEventSynchronize(h->pin_src_ev[slot]));   // a never-recorded event is complete
-        float* p = h->pin_src + static_cast<size_t>(slot) * h->pin_src_floats;
-        std::memcpy(p, vals.data(), sizeof(float) * vals.size());
-        void* dp = nullptr;
-        if (!staged_io() && cudaHostGetDevicePointer(&dp, p, 0) == cudaSuccess) {
-            // the step's kernels read the few values straight from the pinned slot; end_step records the slot's event behind them
-            h->src_vals_mapped = static_cast<const float*>(dp);
-            h->pin_src_inflight = slot;
-        } else {
-            (void)cudaGetLastError();
-            h->src_vals_mapped = nullptr;
-            CU_TRY(h, cudaMemcpyAsync(h->d_src_vals, p, sizeof(float) * vals.size(), cudaMemcpyHostToDevice, h->stream));
-            CU_TRY(h, cudaEventRecord(h->pin_src_ev[slot], h->stream));
-        }
-        h->n_src = m;
-        h->src_rows = 1;
-        h->src_row = 0;
-        return FDTD_B200_OK;
-    }
     h->src_cells_host.clear();
     h->src_vals_mapped = nullptr;
     h->pin_src_inflight = -1;
@@ -1588,6 +1710,9 @@ int fdtd_b200_set_source_table(fdtd_b200_handle h, uint32_t n_src, const uint64_
     CU_TRY(h, cudaMemcpy(h->d_src_cells, lc.data(), sizeof(long long) * m, cudaMemcpyHostToDevice));
     CU_TRY(h, cudaMemcpy(h->d_src_vals, vals.data(), sizeof(float) * vals.size(), cudaMemcpyHostToDevice));
     h->src_cells_host = lc;
+    h->src_cells_raw.assign(raw_cells, raw_cells + n_src);
+    h->src_perm.resize(m);
+    for (uint32_t q = 0; q < m; ++q) h->src_perm[q] = kept[q].second;
     h->n_src = m;
     h->src_rows = n_steps;
     h->src_row = 0;
@@ -1684,7 +1809,7 @@ int fdtd_b200_halo_plane(fdtd_b200_handle h, int which, void** device_ptr, uint6
 
 int fdtd_b200_fused_update(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
-    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle was not created with FDTD_B200_FUSED_STEP (or the lattice is not eligible)");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle does not run the fused step: " + h->fused_why_not);
     if (z_hi > h->nzl || z_lo > z_hi) return fail(h, FDTD_B200_EINVAL, "plane range outside the slab");
     if (int rc = set_device(h)) return rc;
     return launch_fused(h, static_cast<int>(z_lo), static_cast<int>(z_hi));
@@ -1692,7 +1817,7 @@ int fdtd_b200_fused_update(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi) {
 
 int fdtd_b200_fused_commit(fdtd_b200_handle h) {
     if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
-    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle was not created with FDTD_B200_FUSED_STEP (or the lattice is not eligible)");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "handle does not run the fused step: " + h->fused_why_not);
     commit_fused(h);
     return FDTD_B200_OK;
 }
@@ -1754,7 +1879,7 @@ int fdtd_b200_read_field(fdtd_b200_handle h, int component, const uint64_t lo[3]
         CU_TRY(h, cudaMemcpyAsync(out + plane_cells * z * 3, h->d_stage, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
         CU_TRY(h, cudaStreamSynchronize(h->stream));
     }
-    return FDTD_B200_OK;
+    return p2p_poisoned(h);
 }
 
 int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], const float* in) {
@@ -1782,7 +1907,8 @@ int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3
         CU_TRY(h, cudaGetLastError());
         CU_TRY(h, cudaStreamSynchronize(h->stream));
     }
-    return FDTD_B200_OK;
+    h->halos_dirty = true;   // fields written from outside: the neighbours' ghost planes are stale until fdtd_b200_p2p_refresh
+    return p2p_poisoned(h);
 }
 
 int fdtd_b200_device_field(fdtd_b200_handle h, int c, void** device_ptr) {
@@ -1863,9 +1989,10 @@ int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_st
         const bool in_host = h->h_probe_ring && h->row_in_host[first_tick % h->ring_steps];
         const float* src = in_host ? h->h_probe_ring + (first_tick % h->ring_steps) * row : h->pin_probe + pslot * h->pin_probe_floats;
         std::memcpy(out, src, row * sizeof(float));
-        return FDTD_B200_OK;
+        return p2p_poisoned(h);
     }
     CU_TRY(h, cudaStreamSynchronize(h->stream));
+    if (int rc = p2p_poisoned(h)) return rc;
     uint64_t done = 0;
     while (done < n_steps) {
         const uint64_t r = (first_tick + done) % h->ring_steps;
@@ -1912,7 +2039,7 @@ int fdtd_b200_project(fdtd_b200_handle h, int component, const float projection[
         CU_TRY(h, cudaMemcpyAsync(out_rgba, d_out, bytes, cudaMemcpyDeviceToHost, h->stream));
         CU_TRY(h, cudaStreamSynchronize(h->stream));
     }
-    return FDTD_B200_OK;
+    return p2p_poisoned(h);
 }
 
 }  // extern "C"
@@ -2003,7 +2130,7 @@ int scene_launch(fdtd_b200_handle h, const SceneView& V, OutT* out, cudaStream_t
     const int blocks = static_cast<int>(std::min<long long>((quads + 255) / 256, 148LL * 32));
     const size_t smem = static_cast<size_t>(V.n_shapes) * (sizeof(SceneShape) + sizeof(SceneBox));
     auto k = k_rasterize_scene<OutT>;
-    if (smem > 48 * 1024) CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    if (smem > 48 * 1024) if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
     k<<<blocks, 256, smem, st>>>(V, out);
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
@@ -2102,11 +2229,17 @@ struct P2PBlob {
 static_assert(sizeof(P2PBlob) <= FDTD_B200_P2P_BLOB_BYTES, "blob must fit the size the header promises");
 constexpr uint32_t P2P_MAGIC = 0xFD7DB200u;
 
-__global__ void k_wait_flag(const volatile unsigned long long* flag, unsigned long long want, unsigned long long* timeout_marker,
+__global__ void k_wait_flag(const volatile unsigned long long* flag, unsigned long long want, volatile unsigned long long* timeout_marker,
                             long long max_cycles) {
     const long long t0 = clock64();
     while (*flag < want) {
-        if (clock64() - t0 > max_cycles) { atomicExch(timeout_marker, want); return; }   // never hang the GPU; sync() reports it
+        // never hang the GPU: give up after max_cycles and leave a STICKY marker in host memory; later waits return at once and
+        // every host entry point that touches state fails (p2p_poisoned)
+        if (*timeout_marker != 0 || clock64() - t0 > max_cycles) {
+            if (*timeout_marker == 0) *timeout_marker = want;
+            __threadfence_system();
+            return;
+        }
         __nanosleep(200);
     }
     __threadfence_system();   // acquire: the planes pushed before the flag are visible to the kernels that follow
@@ -2218,9 +2351,13 @@ int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st, bool stored_by_kernel
 
 int p2p_wait(fdtd_b200_handle h, cudaStream_t st) {
     if (h->halo_seq == 0) return FDTD_B200_OK;
-    const long long max_cycles = 10LL * 1900000000LL;   // ≈ 10 s at 1.9 GHz
-    if (h->lower.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 0, h->halo_seq, h->d_flags + 2, max_cycles);
-    if (h->upper.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 1, h->halo_seq, h->d_flags + 2, max_cycles);
+    static const long long max_cycles = [] {   // ≈ 10 s at 1.9 GHz; FDTD_B200_P2P_TIMEOUT_MS shortens it (tests)
+        const char* e = std::getenv("FDTD_B200_P2P_TIMEOUT_MS");
+        const long long ms = e ? std::atoll(e) : 0;
+        return (ms > 0 ? ms : 10000LL) * 1900000LL;
+    }();
+    if (h->lower.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 0, h->halo_seq, h->hd_timeout, max_cycles);
+    if (h->upper.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 1, h->halo_seq, h->hd_timeout, max_cycles);
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
 }
@@ -2233,12 +2370,20 @@ int fdtd_b200_p2p_connected(fdtd_b200_handle h) { return h && h->p2p ? 1 : 0; }
 
 int fdtd_b200_p2p_export(fdtd_b200_handle h, void* blob) {
     if (!h || !blob) return fail(h, FDTD_B200_EINVAL, "NULL argument");
-    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport needs a fused-step handle (FDTD_B200_FUSED_STEP on an eligible lattice)");
+    if (!h->fused) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport needs a fused-step handle; this one is not: " + h->fused_why_not);
     if (h->has_pml && !h->pml_in_kernel) return fail(h, FDTD_B200_ESTATE, "the peer-memory transport carries a PML only inside the fused kernel (fdtd_b200_pml_in_kernel); use the two-kernel slab path");
     if (int rc = set_device(h)) return rc;
     if (!h->d_flags) {
         CU_TRY(h, cudaMalloc(&h->d_flags, 64));
         CU_TRY(h, cudaMemset(h->d_flags, 0, 64));
+    }
+    if (!h->h_timeout) {
+        void* hp = nullptr; void* dp = nullptr;
+        CU_TRY(h, cudaHostAlloc(&hp, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+        std::memset(hp, 0, 64);
+        CU_TRY(h, cudaHostGetDevicePointer(&dp, hp, 0));
+        h->h_timeout = static_cast<volatile unsigned long long*>(hp);
+        h->hd_timeout = static_cast<unsigned long long*>(dp);
     }
     // receive buffer for ψ_H of the plane above this slab (the x and y profiles are global, the z entry exists if that plane is a PML coordinate)
     if (h->psi_ghost) { cudaFree(h->psi_ghost); h->psi_ghost = nullptr; }
@@ -2316,19 +2461,31 @@ int fdtd_b200_p2p_connect(fdtd_b200_handle h, const void* lower_blob, const void
     }
     h->p2p = true;
     h->p2p_mat_sent = false;
+    h->halos_dirty = true;   // nothing has been pushed yet: fdtd_b200_p2p_refresh comes first
     return FDTD_B200_OK;
 }
 
 int fdtd_b200_p2p_refresh(fdtd_b200_handle h) {
     if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
     if (int rc = set_device(h)) return rc;
+    if (int rc = p2p_poisoned(h)) return rc;
     // asynchronous and flag-ordered: the next p2p_step's boundary launch waits on the device for the neighbours' copies
+    h->halos_dirty = false;
     return p2p_push(h, h->cur_set, h->stream, false);
 }
 
 int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
     if (!h || !h->p2p) return fail(h, FDTD_B200_ESTATE, "fdtd_b200_p2p_connect has not succeeded on this handle");
     if (int rc = set_device(h)) return rc;
+    if (int rc = p2p_poisoned(h)) return rc;   // sticky: a flag wait of an earlier step timed out
+    if (h->halos_dirty)
+        return fail(h, FDTD_B200_ESTATE, "the neighbours' ghost planes are stale (connect, reset, set_time, write_field or write_pml_state since the last push): "
+                                         "call fdtd_b200_p2p_refresh on every slab first");
+    // Two slabs driven by ONE host thread: a slab's step s+1 waits on the device for its neighbour's step s, which this thread
+    // has not enqueued yet — with several steps per call the launch queue fills behind that wait and the call deadlocks until
+    // the flag wait times out.  One step per call and slab, slabs in turn, is the only order that cannot.
+    if (n_steps > 1 && ((h->lower.present && h->lower.same_process) || (h->upper.present && h->upper.same_process)))
+        return fail(h, FDTD_B200_EINVAL, "neighbour slabs in the same process: call fdtd_b200_p2p_step(h, 1) on each slab in turn");
     const int n = static_cast<int>(h->nzl);
     const HostRowScope scope(h, n_steps == 1);
     const bool split = n >= 3;                      // otherwise the whole slab is "boundary"

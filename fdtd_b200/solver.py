@@ -293,28 +293,57 @@ class FdtdB200Backend:
     """`SolverBackend<FdtdSolverConfig, Point3<usize>>` (lib.rs:28-45) for the CUDA engine."""
 
     def __init__(self, device: int = 0, exact_arithmetic: bool = False, force_generic_kernels: bool = False,
-                 z_slab: Optional[tuple] = None, probe_ring_steps: int = 0, fused_step: bool = False):
+                 z_slab: Optional[tuple] = None, probe_ring_steps: int = 0, fused_step: Optional[bool] = None,
+                 memory_limit: Optional[int] = None):
+        """`fused_step`: None/True = the library's default — the fused single-pass step on ping-pong buffers wherever the
+        lattice is eligible (`FdtdB200SolverState.step_path` says what runs and why); False = two half-step kernels updating
+        the fields in place (FDTD_B200_IN_PLACE_STEP).  `memory_limit` (bytes; `SolverConfigCommon.memory_limit`,
+        cem-app/src/solver/config.rs:27-45): with fused_step=None the fused step is used if its two field sets fit the
+        limit, else the in-place step; `create_instance` raises MemoryError when neither fits, which is where the
+        reference bails (cem-app/src/solver/runner.rs:304-330)."""
         self.device = int(device)
         self.flags = ((L.EXACT_ARITHMETIC if exact_arithmetic else 0) | (L.FORCE_GENERIC_KERNELS if force_generic_kernels else 0)
-                      | (L.FUSED_STEP if fused_step else 0))
+                      | (L.IN_PLACE_STEP if fused_step is False else 0))
+        self.fused_step = fused_step
+        self.memory_limit = None if memory_limit is None else int(memory_limit)
         self.z_slab = z_slab
         self.probe_ring_steps = int(probe_ring_steps)
 
-    def _c_config(self, config: FdtdSolverConfig) -> L.Config:
+    def _c_config(self, config: FdtdSolverConfig, flags: Optional[int] = None) -> L.Config:
         n = config.lattice_size()
         c = L.Config()
         c.nx, c.ny, c.nz = n
         c.dx = (C.c_double * 3)(*config.resolution.spatial)
         c.dt = config.resolution.temporal
         c.device = self.device
-        c.flags = self.flags
+        c.flags = self.flags if flags is None else flags
         c.z_begin, c.z_end = self.z_slab if self.z_slab else (0, 0)
         c.probe_ring_steps = self.probe_ring_steps
         return c
 
     def memory_required(self, config: FdtdSolverConfig, index_bytes: int = 1) -> Optional[int]:
-        cc = self._c_config(config)
+        """`SolverBackend::memory_required` (lib.rs:41-44) in the step mode this backend will use for `config`."""
+        cc = self._c_config(config, self.resolve_flags(config, index_bytes, enforce=False))
         return int(L.lib().fdtd_b200_memory_required(C.byref(cc), index_bytes)) or None
+
+    def resolve_flags(self, config: FdtdSolverConfig, index_bytes: int = 1, enforce: bool = True) -> int:
+        """Config flags after the memory_limit decision (fdtd_b200_choose_step_mode): fused if it fits, else in place."""
+        if self.memory_limit is None or self.fused_step is not None:
+            if enforce and self.memory_limit is not None:
+                cc = self._c_config(config)
+                need = int(L.lib().fdtd_b200_memory_required(C.byref(cc), index_bytes))
+                if need > self.memory_limit:
+                    raise MemoryError(f"lattice needs {need} bytes of device memory, memory_limit is {self.memory_limit}")
+            return self.flags
+        cc = self._c_config(config)
+        flags, need = C.c_uint32(0), C.c_uint64(0)
+        rc = L.lib().fdtd_b200_choose_step_mode(C.byref(cc), index_bytes, self.memory_limit, C.byref(flags), C.byref(need))
+        if rc == L.ENOMEM:
+            if enforce:
+                raise MemoryError(f"lattice needs {need.value} bytes of device memory, memory_limit is {self.memory_limit}")
+            return self.flags | L.IN_PLACE_STEP
+        L.check(rc)
+        return int(flags.value)
 
     def create_instance(self, config: FdtdSolverConfig, domain_description: DomainDescription) -> "FdtdB200SolverInstance":
         n = config.lattice_size()
@@ -380,7 +409,8 @@ class FdtdB200SolverInstance:
     # -- SolverInstance -------------------------------------------------------------------------
     def create_state(self) -> "FdtdB200SolverState":
         lib = L.lib()
-        cc = self.backend._c_config(self.config)
+        index_bytes = 1 if len(self.palette) + 1 <= 256 else 2   # + the pad row of padded lattices (conservative)
+        cc = self.backend._c_config(self.config, self.backend.resolve_flags(self.config, index_bytes))
         pc = L.PhysicalConstants(self.config.physical_constants.vacuum_permittivity, self.config.physical_constants.vacuum_permeability)
         pal = (L.Material * len(self.palette))(*[L.Material(*m.as_row()) for m in self.palette])
         idp = None if self.ids is None else self.ids.ctypes.data_as(C.POINTER(C.c_uint32))
@@ -638,6 +668,17 @@ class FdtdB200SolverState:
     @property
     def kernel_launches(self) -> int:
         return int(self._lib.fdtd_b200_kernel_launches(self._h))
+
+    @property
+    def step_path(self) -> str:
+        """Which kernels `step` launches on this handle and why (fdtd_b200_step_path) — there are no silent fallbacks."""
+        buf = C.create_string_buffer(512)
+        self._lib.fdtd_b200_step_path(self._h, buf, len(buf))
+        return buf.value.decode()
+
+    @property
+    def memory_in_use(self) -> int:
+        return int(self._lib.fdtd_b200_memory_in_use(self._h))
 
 
 class FdtdB200UpdatePass:

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define FDTD_B200_ABI_VERSION 1
+#define FDTD_B200_ABI_VERSION 2
 
 typedef struct fdtd_b200_solver* fdtd_b200_handle;
 
@@ -49,11 +49,16 @@ enum {
     FDTD_B200_EXACT_ARITHMETIC = 1u << 0,
     /* Force the one-thread-per-cell kernels even when nx % 4 == 0 (debugging / bisecting). */
     FDTD_B200_FORCE_GENERIC_KERNELS = 1u << 1,
-    /* fdtd_b200_step() runs ONE fused kernel per step (H and E half-steps in a single pass over the lattice,
-       49 B instead of 74 B per cell update) on ping-pong field buffers: +24 B/cell of device memory.  Results are
-       bit-identical to the two-kernel path.  Ignored (two-kernel path) for z-slab handles and for lattices the
-       fused kernel does not support (nx not a multiple of 16 index bytes, nx < 128). */
-    FDTD_B200_FUSED_STEP = 1u << 2
+    /* Accepted for source compatibility with ABI 1 and ignored: the fused single-pass step is the DEFAULT since ABI 2. */
+    FDTD_B200_FUSED_STEP = 1u << 2,
+    /* Step kernel selection.  `SolverBackend::create_instance` (lib.rs:28-45) has no knob for it, so the library decides:
+       by default fdtd_b200_step() runs ONE fused kernel per step (H and E half-steps in a single pass over the lattice,
+       49 B instead of 74 B of HBM traffic per cell update) on ping-pong field buffers, i.e. +24 B/cell of device memory,
+       whenever the lattice is eligible (row pitch >= 128 cells).  This flag opts out: two half-step kernels updating
+       the fields in place (24 B/cell of field memory).  Results are bit-identical either way.  A caller with a memory
+       budget (cem-app/src/solver/runner.rs:304-330 `memory_limit`) asks fdtd_b200_choose_step_mode() which of the two
+       fits; fdtd_b200_step_path() reports what a handle runs and why. */
+    FDTD_B200_IN_PLACE_STEP = 1u << 3
 };
 
 /* cem-solver/src/material.rs:105-116 (same field order). */
@@ -134,9 +139,18 @@ int fdtd_b200_canonicalize_material_index(const uint32_t* ids_in, uint64_t n_cel
                                           uint32_t n_palette_in, uint32_t* ids_out, fdtd_b200_material* palette_out,
                                           uint32_t palette_cap, uint32_t* n_palette_out);
 
-/* `SolverBackend::memory_required` (lib.rs:41-44; cpu/mod.rs:217-221; wgpu/mod.rs:129-133): device
- * bytes a handle for `cfg` will allocate with an index of `index_bytes` (1 or 2) per cell. */
+/* `SolverBackend::memory_required` (lib.rs:41-44; cpu/mod.rs:217-221; wgpu/mod.rs:129-133): device bytes of the fields and
+ * the material index a handle for `cfg` will allocate with an index of `index_bytes` (1 or 2) per cell, in the step mode
+ * cfg->flags selects (fused: two field sets unless FDTD_B200_IN_PLACE_STEP is set or the lattice is not eligible).  This is
+ * the per-cell part; probe rings, PML psi arrays and forcing tables come on top (fdtd_b200_memory_in_use reports the total
+ * of a live handle). */
 size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_bytes);
+/* What cem-app/src/solver/runner.rs:304-330 does with `memory_limit`, for a backend with two step modes: the fused step if
+ * its memory fits `memory_limit` bytes (0 = no limit), else the in-place two-kernel step, else ENOMEM.  *flags_out =
+ * cfg->flags with FDTD_B200_IN_PLACE_STEP set or cleared accordingly, *required_out = fdtd_b200_memory_required of that
+ * mode (also on ENOMEM: the smaller of the two). */
+int fdtd_b200_choose_step_mode(const fdtd_b200_config* cfg, uint32_t index_bytes, uint64_t memory_limit, uint32_t* flags_out,
+                               uint64_t* required_out);
 
 /* ---- instance / state ---------------------------------------------------------------------- */
 
@@ -203,6 +217,12 @@ int fdtd_b200_read_pml_state(fdtd_b200_handle h, float* out);
 int fdtd_b200_write_pml_state(fdtd_b200_handle h, const float* in);
 
 /* Introspection used by tests and the bench. */
+/* Device bytes this handle holds right now (fields, index, table, forcing, probe ring, psi, staging) — cudaMalloc sizes. */
+uint64_t fdtd_b200_memory_in_use(fdtd_b200_handle h);
+/* Which kernels fdtd_b200_step() launches on this handle and why, e.g. "fused: k_step_fused<fast,u8>" or
+ * "two-kernel (bulk): in-place step requested (FDTD_B200_IN_PLACE_STEP)" or "two-kernel (vec4): row pitch 64 < 128 cells".
+ * Writes at most cap bytes including the terminating NUL; returns the full length. */
+int fdtd_b200_step_path(fdtd_b200_handle h, char* buf, size_t cap);
 int fdtd_b200_index_bytes(fdtd_b200_handle h);   /* 1 or 2 */
 int fdtd_b200_uses_vec4(fdtd_b200_handle h);     /* 1 when the float4 z-streaming kernels run */
 int fdtd_b200_uses_bulk(fdtd_b200_handle h);     /* 1 when the TMA bulk-copy staged kernels run */
@@ -245,7 +265,7 @@ int fdtd_b200_update_h(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
 int fdtd_b200_update_e(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);
 /* tick += 1, time += dt, consume one forcing row, advance the probe ring. */
 int fdtd_b200_end_step(fdtd_b200_handle h);
-/* Fused-step handles (FDTD_B200_FUSED_STEP): update planes [z_lo, z_hi) with the single-pass kernel, reading the current
+/* Fused-step handles (fdtd_b200_uses_fused): update planes [z_lo, z_hi) with the single-pass kernel, reading the current
  * buffer set (incl. ghost planes) and writing the pending one; launches of disjoint ranges are independent.  commit
  * makes the pending set current (call once per step after every plane was updated, then fdtd_b200_end_step). */
 int fdtd_b200_fused_update(fdtd_b200_handle h, uint64_t z_lo, uint64_t z_hi);

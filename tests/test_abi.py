@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol(b200):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/fdtd_b200.h but not exported"
     assert set(names) == set(_lib.SYMBOLS), "ctypes binding and header disagree"
-    assert lib.fdtd_b200_abi_version() == 1
+    assert lib.fdtd_b200_abi_version() == _lib.ABI_VERSION == 2
 
 
 def test_struct_layouts(b200):
@@ -107,15 +107,50 @@ def test_canonicalize_matches_per_cell_indexing(b200, oracle):
 
 def test_memory_required(b200):
     cfg = b200.FdtdSolverConfig.from_lattice((512, 512, 512), b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED)
-    be = b200.FdtdB200Backend()
+    be = b200.FdtdB200Backend(fused_step=False)
     need = be.memory_required(cfg)
     cells = 512 ** 3
     assert need == 24 * 512 * 512 * 514 + cells + 512 * 512 + 16      # fields (+2 ghost planes) + u8 index (+1 plane)
     assert need / cells < 26                      # vs 136 B/cell (cpu/mod.rs:217-221) and 80 B/cell (wgpu/mod.rs:129-133)
     assert be.memory_required(cfg, 2) == need + cells + 512 * 512
-    assert b200.FdtdB200Backend(fused_step=True).memory_required(cfg) == need + 24 * 512 * 512 * 514   # ping-pong set
-    slab = b200.FdtdB200Backend(z_slab=(128, 256))
+    # the default backend runs the fused step: ping-pong field sets
+    assert b200.FdtdB200Backend().memory_required(cfg) == need + 24 * 512 * 512 * 514
+    assert b200.FdtdB200Backend(fused_step=True).memory_required(cfg) == need + 24 * 512 * 512 * 514
+    slab = b200.FdtdB200Backend(z_slab=(128, 256), fused_step=False)
     assert slab.memory_required(cfg) == 24 * 512 * 512 * 130 + 512 * 512 * 129 + 16
+
+
+def test_memory_limit_picks_the_step_mode(b200):
+    """cem-app/src/solver/runner.rs:304-330: memory_required is checked against memory_limit before construction.  With two
+    step modes the backend takes the fused step if its two field sets fit the limit, else the in-place step, else it bails."""
+    from fdtd_b200 import _lib as L
+
+    lib = b200.lib()
+    cfg = b200.FdtdSolverConfig.from_lattice((512, 512, 512), b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED)
+    fused = b200.FdtdB200Backend().memory_required(cfg)
+    in_place = b200.FdtdB200Backend(fused_step=False).memory_required(cfg)
+    assert in_place < fused
+    roomy, tight, tiny = b200.FdtdB200Backend(memory_limit=fused), b200.FdtdB200Backend(memory_limit=fused - 1), b200.FdtdB200Backend(memory_limit=in_place - 1)
+    assert roomy.resolve_flags(cfg) & L.IN_PLACE_STEP == 0 and roomy.memory_required(cfg) == fused
+    assert tight.resolve_flags(cfg) & L.IN_PLACE_STEP and tight.memory_required(cfg) == in_place
+    with pytest.raises(MemoryError):
+        tiny.resolve_flags(cfg)
+    with pytest.raises(MemoryError):          # before anything touches a device, like the reference's bail
+        tiny.create_instance(cfg, b200.MaterialLattice([b200.Material.VACUUM])).create_state()
+    with pytest.raises(MemoryError):          # an explicit mode is not overridden, only checked
+        b200.FdtdB200Backend(fused_step=True, memory_limit=fused - 1).resolve_flags(cfg)
+    # the C entry point itself
+    cc = b200.FdtdB200Backend()._c_config(cfg)
+    flags, need = C.c_uint32(99), C.c_uint64(0)
+    assert lib.fdtd_b200_choose_step_mode(C.byref(cc), 1, 0, C.byref(flags), C.byref(need)) == L.OK and flags.value == 0 and need.value == fused
+    assert lib.fdtd_b200_choose_step_mode(C.byref(cc), 1, fused - 1, C.byref(flags), C.byref(need)) == L.OK
+    assert flags.value == L.IN_PLACE_STEP and need.value == in_place
+    assert lib.fdtd_b200_choose_step_mode(C.byref(cc), 1, 1000, C.byref(flags), C.byref(need)) == L.ENOMEM and need.value == in_place
+    assert lib.fdtd_b200_choose_step_mode(C.byref(cc), 3, 0, C.byref(flags), C.byref(need)) == L.EINVAL
+    # the app's canned configs (cem-app/src/composer/mod.rs:841-869): 100x100x1 under memory_limit = 200 MB -> fused (pitch 128)
+    app = b200.FdtdSolverConfig.from_lattice((100, 100, 1), b200.Resolution((0.01, 0.01, 0.01), 0.001), b200.PhysicalConstants.REDUCED)
+    be = b200.FdtdB200Backend(memory_limit=200_000_000)
+    assert be.resolve_flags(app) & L.IN_PLACE_STEP == 0 and be.memory_required(app) == 12 * 4 * 128 * 100 * 3 + 128 * 100 * 2 + 16
 
 
 def test_invalid_configs_are_rejected_without_a_device(b200):
@@ -171,14 +206,16 @@ def test_memory_required_counts_the_row_pitch(b200, monkeypatch):
     def need(nx, **kw):
         return b200.FdtdB200Backend(**kw).memory_required(b200.FdtdSolverConfig.from_lattice((nx, 10, 8), res, pc))
 
-    def expect(pitch, fused=False):
+    def expect(pitch, fused=None):
         plane = pitch * 10
+        fused = pitch >= 128 if fused is None else fused              # the default step mode: fused wherever eligible
         return (12 if fused else 6) * 4 * plane * 10 + plane * 9 + 16
 
     assert need(150) == expect(160) and need(509) == expect(512) and need(100) == expect(128) and need(97) == expect(128)
     assert need(96) == expect(96) and need(160) == expect(160) and need(63) == expect(63) and need(65) == expect(80)
-    assert need(150, fused_step=True) == expect(160, fused=True)          # pitch >= 128: two buffer sets
-    assert need(70, fused_step=True) == expect(80)                        # pitch < 128: the fused kernel is not eligible
-    assert need(150, force_generic_kernels=True) == expect(150)
+    assert need(150) == expect(160, fused=True)                           # pitch >= 128: two buffer sets
+    assert need(150, fused_step=False) == expect(160, fused=False)        # FDTD_B200_IN_PLACE_STEP
+    assert need(70, fused_step=True) == expect(80, fused=False)           # pitch < 128: the fused kernel is not eligible
+    assert need(150, force_generic_kernels=True) == expect(150, fused=False)
     monkeypatch.setenv("FDTD_B200_NO_ROW_PADDING", "1")
-    assert need(150) == expect(150)
+    assert need(150) == expect(150, fused=False)                          # 150 % 4 != 0: one-thread-per-cell kernels, in place

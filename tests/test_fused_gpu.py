@@ -96,10 +96,12 @@ def test_fused_u16_index_and_fallbacks(b200, oracle, tune):
     assert st.uses_fused and st.index_bytes == 2
     assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
     assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.field(oracle.H).astype(np.float32))
-    # lattices the fused kernel does not support silently use the two-kernel path
+    assert st.step_path.startswith("fused: k_step_fused<exact,u16>")
+    # lattices the fused kernel does not support use the two-kernel path, and the handle says why
     w2 = _random_workload(b200, (36, 5, 4), seed=2)
     st2, _ = run(b200, w2, 2, exact=True, fused=True)
     assert not st2.uses_fused and st2.tick() == 2
+    assert st2.step_path.startswith("two-kernel (vec4)") and "row pitch 36 < 128" in st2.step_path
 
 
 @pytest.mark.parametrize("size,cut,ranges", [((128, 9, 10), 6, "whole"), ((256, 5, 9), 4, "split"), ((128, 8, 5), 1, "whole")])
@@ -213,9 +215,10 @@ def test_p2p_argument_errors(b200, tune):
 
     tune(None)
     w = _random_workload(b200, (128, 8, 8), seed=3)
-    plain = b200.FdtdB200Backend(z_slab=(0, 4)).create_instance(w.solver_config(), w.domain()).create_state()
-    with pytest.raises(L.Fdtd_b200Error):
+    plain = b200.FdtdB200Backend(z_slab=(0, 4), fused_step=False).create_instance(w.solver_config(), w.domain()).create_state()
+    with pytest.raises(L.Fdtd_b200Error) as ei:
         plain.p2p_export()                                   # not a fused-step handle
+    assert "FDTD_B200_IN_PLACE_STEP" in str(ei.value)
     a = b200.FdtdB200Backend(fused_step=True, z_slab=(0, 4)).create_instance(w.solver_config(), w.domain()).create_state()
     b = b200.FdtdB200Backend(fused_step=True, z_slab=(5, 8)).create_instance(w.solver_config(), w.domain()).create_state()
     with pytest.raises(L.Fdtd_b200Error):
