@@ -66,6 +66,7 @@ struct fdtd_b200_solver {
     std::string fused_why_not;      // why this handle is not on the fused step (empty when it is); fdtd_b200_step_path
     FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
     bool fused_maps_ready = false;
+    int zc_override = 0;            // planes per CTA march forced for the next fused launches (fdtd_b200_p2p_step's chunk-aligned split)
     int n_sm = 0;                   // SMs of the device (queried at the first fused launch)
     int sm_smem_bytes = 0, sm_smem_reserved = 0;   // shared memory per SM / reserved per CTA (queried at the first fused launch)
     int cur_set = 0;                // which buffer set f[] currently points at
@@ -531,7 +532,7 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
 // partly idle for ≈ 0.43 of a march: cost(zc) = (ceil(tiles · chunks / slots) + 0.43) · (zc + c) with balanced chunks.
 // c and 0.43 are fitted to tools/exp_zc_midsize.sh (profiles/r01_exp_zc_midsize.txt: 256³ best at 16 planes, 384³ at 24,
 // 512³ at 32..64, 128 slower than the model says); the previous rule (halve 64 until 3 waves exist) left 384³ at 64 planes, 10 % slower.
-int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes) {
+int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunks = 1) {
     if (h->n_sm == 0) {
         if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
     }
@@ -542,6 +543,7 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes) {
     for (int zc : cand) {
         if (zc > planes && zc != cand[0]) { if (best_cost < 1e300) break; }
         const int chunks = (planes + zc - 1) / zc;
+        if (chunks < min_chunks) continue;                // the peer-memory split wants a chunk per boundary plus an interior
         const int zce = (planes + chunks - 1) / chunks;   // balanced
         const double cost = (std::ceil(static_cast<double>(tiles) * chunks / slots) + 0.43) * (zce + 2.5);
         if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = zce; }
@@ -599,7 +601,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     for (int a = 0; a < 3; ++a) { V.dx[a] = static_cast<float>(h->cfg.dx[a]); V.inv_dx[a] = 1.0f / V.dx[a]; }
     const ForcingView F = forcing_view(h);
     const ProbeView P = probe_view(h);
-    int zc = h->tune.zc;
+    int zc = h->zc_override > 0 ? h->zc_override : h->tune.zc;
     if (zc <= 0) {
         const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS);
         zc = pick_fused_zc(h, tiles, z_hi - z_lo);
@@ -2488,9 +2490,27 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
         return fail(h, FDTD_B200_EINVAL, "neighbour slabs in the same process: call fdtd_b200_p2p_step(h, 1) on each slab in turn");
     const int n = static_cast<int>(h->nzl);
     const HostRowScope scope(h, n_steps == 1);
+    // Split of the slab into the boundary launches (high-priority stream: their stores into the neighbours' ghost planes leave
+    // early in the step) and the interior launch (main stream).  The boundary launches are WHOLE CHUNKS of the march a single
+    // launch over the slab would make — [0, zc) and [n - zc, n) — so the step pays exactly as many ring prologues and
+    // recomputed H' planes as an unsplit step.  (Round 1 launched the two boundary PLANES on their own: a one-plane march is all
+    // prologue, ≈ 3.5 plane-times each, 4 % of a 128-plane slab — the named limiter of the 1→8 weak-scaling curve.)  Slabs too
+    // thin for three chunks fall back to one-plane boundary launches, slabs under three planes are all boundary.
+    static const bool plane_split = [] { const char* e = std::getenv("FDTD_B200_P2P_PLANE_SPLIT"); return e && e[0] == '1'; }();
+    int zc_chunk = 0;
+    if (!plane_split && n >= 3) {
+        constexpr int BX = 32, BYc = 7;   // tile of k_step_fused<…, 32, 8>: 128 cells × 7 core rows
+        const long long tiles = static_cast<long long>((h->nx + 4 * BX - 1) / (4 * BX)) * ((h->ny + BYc - 1) / BYc);
+        const int n_bnd = (h->lower.present ? 1 : 0) + (h->upper.present ? 1 : 0);
+        const int zc_full = h->tune.zc > 0 ? h->tune.zc : pick_fused_zc(h, tiles, n, n_bnd + 1);
+        if (zc_full * n_bnd < n) zc_chunk = zc_full;
+    }
     const bool split = n >= 3;                      // otherwise the whole slab is "boundary"
-    const int lo = (split && h->lower.present) ? 1 : 0;
-    const int hi = (split && h->upper.present) ? n - 1 : n;
+    const int bw = zc_chunk > 0 ? zc_chunk : 1;     // planes per boundary launch
+    const int lo = (split && h->lower.present) ? bw : 0;
+    const int hi = (split && h->upper.present) ? n - bw : n;
+    struct ZcScope { fdtd_b200_handle h; ~ZcScope() { h->zc_override = 0; } } zc_scope{h};
+    h->zc_override = zc_chunk;
     cudaStream_t S = h->stream, B = h->bstream;
     // default: the boundary CTAs store into the neighbours' ghost planes themselves; FDTD_B200_P2P_COPY_ENGINE=1 selects
     // the earlier variant (seven peer cudaMemcpyAsync per step and cut after the boundary kernels) for comparison
