@@ -20,6 +20,7 @@
 #include "kernels_fused.cuh"
 #include "kernels_scene.cuh"
 #include "kernels_pml.cuh"
+#include "kernels_resident.cuh"
 
 using namespace fdtd_b200;
 
@@ -66,6 +67,11 @@ struct fdtd_b200_solver {
     std::string fused_why_not;      // why this handle is not on the fused step (empty when it is); fdtd_b200_step_path
     FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
     bool fused_maps_ready = false;
+    int resident = -1;              // -1 not decided | 0 no | 1 one thread-block cluster | 2 cooperative grid (k_steps_resident)
+    std::string resident_why_not;
+    unsigned long long* d_sync = nullptr;      // grid-barrier slots of the resident kernel (one per CTA), epochs keep counting across launches
+    unsigned long long sync_epoch = 0;
+    int resident_ctas = 0, resident_cpt = 1;   // CTAs of the resident launch, cells per thread
     int zc_override = 0;            // planes per CTA march forced for the next fused launches (fdtd_b200_p2p_step's chunk-aligned split)
     int n_sm = 0;                   // SMs of the device (queried at the first fused launch)
     int sm_smem_bytes = 0, sm_smem_reserved = 0;   // shared memory per SM / reserved per CTA (queried at the first fused launch)
@@ -100,6 +106,7 @@ struct fdtd_b200_solver {
 
     // probes
     long long* d_probe_cells = nullptr;
+    std::vector<long long> probe_cells_host;   // what d_probe_cells holds (sorted local indices)
     int* d_probe_slot = nullptr;
     float* d_probe_ring = nullptr;  // [ring_steps][n_probes_total][6]
     // One-step calls (fdtd_b200_step(h, 1), fdtd_b200_p2p_step(h, 1): the reference's per-step protocol) write their probe row
@@ -657,6 +664,7 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
 // boundary: the recomputed column right of a tile then advances its own x-slab ψ_H from the current set).  FDTD_B200_PML_PASSES=1 forces
 // the passes (the two ways agree bit for bit: tests/test_pml_gpu.py).
 void pml_refresh_mode(fdtd_b200_handle h) {
+    h->resident = -1;   // a CPML changes whether the L2-resident multi-step kernel may run (decided again at the next step)
     h->pml_in_kernel = false;
     if (!h->has_pml || !h->fused) return;
     if (const char* e = std::getenv("FDTD_B200_PML_PASSES")) if (e[0] == '1') return;
@@ -953,6 +961,187 @@ void end_step(fdtd_b200_handle h) {
         h->src_row += 1;
         if (h->src_row >= h->src_rows) { h->n_src = 0; h->src_rows = 0; h->src_row = 0; h->src_vals_mapped = nullptr; }  // forcing is per step (cpu/mod.rs:370-377)
     }
+}
+
+// ---- L2-resident lattices: one persistent launch for n steps (kernels_resident.cuh) --------------------------------------------
+// Decided at the first step (and again after anything that changes eligibility).  Eligible: a whole lattice (no slab
+// neighbours), no CPML, at most n_sm × 512 × 4 cells (every thread of one CTA per SM keeps ≤ 4 cells in registers: 303 104 cells on
+// 148 SMs; FDTD_B200_RESIDENT_MAX_CELLS lowers it), kernel choice not forced by flags / FDTD_B200_TUNE, FDTD_B200_RESIDENT != 0.
+template <int EXACT, typename IdxT, int CPT>
+int launch_resident_c(fdtd_b200_handle h, const ResidentView& V) {
+    void* args[] = {const_cast<ResidentView*>(&V)};
+    if (h->resident == 1) {
+        if constexpr (CPT <= 2) {
+            auto k = k_steps_cluster<EXACT, IdxT, CPT>;   // fields in distributed shared memory
+            if (h->resident_ctas > 8) {
+                static std::mutex mu; static std::map<std::pair<int, const void*>, bool> done;
+                std::lock_guard<std::mutex> lock(mu);
+                auto key = std::make_pair(h->device, reinterpret_cast<const void*>(k));
+                if (!done[key]) { CU_TRY(h, cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); done[key] = true; }
+            }
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(h->resident_ctas, 1, 1);
+            cfg.blockDim = dim3(kResidentThreads, 1, 1);
+            cfg.dynamicSmemBytes = 0;
+            cfg.stream = h->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = h->resident_ctas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            CU_TRY(h, cudaLaunchKernelEx(&cfg, k, V));
+        } else {
+            return fail(h, FDTD_B200_ESTATE, "the cluster regime keeps at most 2 cells per thread");
+        }
+    } else {
+        auto k = k_steps_resident<EXACT, IdxT, false, CPT>;
+        CU_TRY(h, cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k), dim3(h->resident_ctas, 1, 1), dim3(kResidentThreads, 1, 1), args, 0, h->stream));
+    }
+    h->launches += 1;
+    return FDTD_B200_OK;
+}
+
+template <int EXACT, typename IdxT>
+int launch_resident_t(fdtd_b200_handle h, const ResidentView& V) {
+    switch (h->resident_cpt) {
+        case 1: return launch_resident_c<EXACT, IdxT, 1>(h, V);
+        case 2: return launch_resident_c<EXACT, IdxT, 2>(h, V);
+        default: return launch_resident_c<EXACT, IdxT, 4>(h, V);
+    }
+}
+
+// CTAs of 512 threads × cpt cells that cover n cells, for the smallest cpt in {1, 2, 4} that needs at most max_ctas; 0 if none does
+int resident_shape(long long n, int max_ctas, int max_cpt, int* cpt_out) {
+    for (int cpt : {1, 2, 4}) {
+        if (cpt > max_cpt) break;
+        const long long ctas = (n + static_cast<long long>(kResidentThreads) * cpt - 1) / (static_cast<long long>(kResidentThreads) * cpt);
+        if (ctas <= max_ctas) { *cpt_out = cpt; return static_cast<int>(std::max<long long>(ctas, 1)); }
+    }
+    return 0;
+}
+
+void resident_decide(fdtd_b200_handle h, bool allow_cluster = true) {
+    h->resident = 0;
+    h->resident_ctas = 0;
+    h->resident_why_not.clear();
+    auto no = [&](const std::string& why) { h->resident_why_not = why; };
+    if (const char* e = std::getenv("FDTD_B200_RESIDENT")) if (e[0] == '0') return no("FDTD_B200_RESIDENT=0");
+    if (h->flags & FDTD_B200_FORCE_GENERIC_KERNELS) return no("FDTD_B200_FORCE_GENERIC_KERNELS");
+    if (h->tune.variant >= 0 || h->tune.zc > 0 || h->tune.bx > 0) return no("FDTD_B200_TUNE forces a kernel variant");
+    if (h->z_begin != 0 || h->z_end != h->nz) return no("z-slab handle");
+    if (h->has_pml) return no("CPML");
+    if (h->n_sm == 0) {
+        if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
+    }
+    const long long n = static_cast<long long>(h->n_local);
+    long long max_cells = static_cast<long long>(h->n_sm) * kResidentThreads * 4;
+    if (const char* e = std::getenv("FDTD_B200_RESIDENT_MAX_CELLS")) max_cells = std::min<long long>(max_cells, std::atoll(e));
+    if (n > max_cells) return no("lattice state does not fit the on-chip budget (" + std::to_string(n) + " cells > " + std::to_string(max_cells) + ")");
+    int cpt = 0;
+    if (allow_cluster) {
+        if (const int ctas = resident_shape(n, 16, 2, &cpt)) {   // one thread-block cluster: fields in distributed shared memory, hardware barrier
+            h->resident = 1; h->resident_ctas = ctas; h->resident_cpt = cpt;
+            return;
+        }
+    }
+    int coop = 0;
+    if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device) != cudaSuccess || !coop) { (void)cudaGetLastError(); return no("device does not support cooperative launches"); }
+    if (const int ctas = resident_shape(n, h->n_sm, 4, &cpt)) { h->resident = 2; h->resident_ctas = ctas; h->resident_cpt = cpt; return; }
+    no("lattice does not fit one CTA per SM");
+}
+
+bool resident_now(fdtd_b200_handle h) {
+    if (h->resident < 0) resident_decide(h);
+    return h->resident > 0;
+}
+
+void end_step(fdtd_b200_handle h);
+int probe_mirror_row(fdtd_b200_handle h, uint64_t tick);
+
+// n steps in one launch (chunks of at most 4096 steps, the default probe ring)
+int step_resident(fdtd_b200_handle h, uint64_t n_steps) {
+    const int mode = arithmetic_mode(h);
+    uint64_t done = 0;
+    while (done < n_steps) {
+        int chunk = static_cast<int>(std::min<uint64_t>(n_steps - done, std::max<uint32_t>(std::min<uint32_t>(h->ring_steps, 4096u), 1u)));
+        if (h->resident == 1 && h->n_probes_local) {   // the cluster kernel stages its probe rows in shared memory until the launch ends
+            const long long cells_per_cta = static_cast<long long>(kResidentThreads) * h->resident_cpt;
+            size_t busiest = 1, run = 0; long long cta = -1;
+            for (long long c : h->probe_cells_host) {
+                if (c / cells_per_cta != cta) { cta = c / cells_per_cta; run = 0; }
+                busiest = std::max(busiest, ++run);
+            }
+            chunk = std::max(1, std::min<int>(chunk, static_cast<int>(kProbeStageFloats / (6 * busiest))));
+            if (6 * busiest > static_cast<size_t>(kProbeStageFloats)) {   // more probes in one CTA than the staging area holds: grid regime
+                resident_decide(h, false);
+                if (h->resident != 2) return -1;
+                continue;
+            }
+        }
+        ResidentView V{};
+        V.L = lattice_view(h);
+        V.n_steps = chunk;
+        const ForcingView F = forcing_view(h);
+        V.n_src = F.n; V.src_cells = F.cells; V.src_vals = F.vals;
+        V.src_rows = F.n ? static_cast<int>(std::min<uint64_t>(h->src_rows - h->src_row, static_cast<uint64_t>(chunk))) : 0;
+        if (h->n_probes_local) {
+            V.n_probes = static_cast<int>(h->n_probes_local);
+            V.probe_cells = h->d_probe_cells; V.probe_slot = h->d_probe_slot;
+            V.ring = (h->probe_rows_to_host && h->hd_probe_ring) ? h->hd_probe_ring : h->d_probe_ring;
+            V.tick0 = h->tick; V.ring_steps = h->ring_steps; V.n_probes_total = h->n_probes_total;
+        }
+        if (h->resident == 2 && !h->d_sync) {
+            CU_TRY(h, cudaMalloc(&h->d_sync, sizeof(unsigned long long) * 1024));
+            CU_TRY(h, cudaMemsetAsync(h->d_sync, 0, sizeof(unsigned long long) * 1024, h->stream));
+        }
+        V.sync_flags = h->d_sync;
+        V.epoch0 = h->sync_epoch;
+        static const int barrier_mode = [] { const char* e = std::getenv("FDTD_B200_RESIDENT_BARRIER"); return e ? std::atoi(e) : 0; }();
+        V.barrier_mode = barrier_mode;
+        static const bool debug = [] { const char* e = std::getenv("FDTD_B200_RESIDENT_DEBUG"); return e && e[0] == '1'; }();
+        long long* d_dbg = nullptr;
+        if (debug) {
+            CU_TRY(h, cudaMalloc(&d_dbg, sizeof(long long) * 64 * 1024));
+            CU_TRY(h, cudaMemsetAsync(d_dbg, 0, sizeof(long long) * 64 * 1024, h->stream));
+            V.dbg = d_dbg;
+        }
+        if (int rcp = prof_begin(h, 0, static_cast<int>(h->nzl) * chunk)) return rcp;   // one event pair per launch; cells = lattice × steps
+        int rc;
+        if (h->idx_bytes == 1) rc = mode == 0 ? launch_resident_t<0, uint8_t>(h, V) : (mode == 1 ? launch_resident_t<1, uint8_t>(h, V) : launch_resident_t<2, uint8_t>(h, V));
+        else rc = mode == 0 ? launch_resident_t<0, uint16_t>(h, V) : (mode == 1 ? launch_resident_t<1, uint16_t>(h, V) : launch_resident_t<2, uint16_t>(h, V));
+        if (rc) {
+            if (done != 0) return rc;
+            (void)cudaGetLastError();
+            if (h->resident == 1) {   // the cluster shape was refused (cluster size / free SMs of a GPC): same kernel, grid barrier
+                const std::string why = h->err;
+                resident_decide(h, false);
+                if (h->resident == 2) continue;
+                h->err = why;
+            }
+            // e.g. the cooperative launch does not fit next to other work: the streaming kernels take over for good, and step_path says so
+            h->resident = 0;
+            h->resident_why_not = "resident launch refused: " + h->err;
+            return -1;
+        }
+        if (int rcp = prof_end(h, 0)) return rcp;
+        if (d_dbg) {   // diagnostic: where thread 0 of every CTA spends a step (cycles): H compute | barrier | E compute | barrier
+            std::vector<long long> t(64 * 1024);
+            CU_TRY(h, cudaStreamSynchronize(h->stream));
+            CU_TRY(h, cudaMemcpy(t.data(), d_dbg, sizeof(long long) * t.size(), cudaMemcpyDeviceToHost));
+            cudaFree(d_dbg);
+            double acc[4] = {0, 0, 0, 0}; int cnt = 0;
+            for (int c = 0; c < h->resident_ctas; ++c)
+                for (int st = 1; st < std::min(chunk, 8) - 1; ++st) {
+                    const long long* q = &t[(c * 8 + st) * 8];
+                    acc[0] += q[2] - q[0]; acc[1] += q[3] - q[2]; acc[2] += q[6] - q[3]; acc[3] += q[7] - q[6]; ++cnt;
+                }
+            if (cnt) std::fprintf(stderr, "[fdtd_b200 resident debug] ctas=%d cpt=%d mode=%d  H phase %.0f | barrier %.0f | E phase %.0f | barrier %.0f cycles (thread 0, mean over CTAs and steps 1..6)\n",
+                                  h->resident_ctas, h->resident_cpt, h->resident, acc[0] / cnt, acc[1] / cnt, acc[2] / cnt, acc[3] / cnt);
+        }
+        h->sync_epoch += 2ull * chunk;
+        for (int s = 0; s < chunk; ++s) end_step(h);
+        done += chunk;
+    }
+    return FDTD_B200_OK;
 }
 
 // Sticky failure of the peer-memory transport (fdtd_b200_solver::h_timeout).  Cheap: one read of host memory.
@@ -1271,6 +1460,7 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (h->bstream) cudaStreamSynchronize(h->bstream);
     for (auto* link : {&h->lower, &h->upper}) { for (void* p : link->opened) cudaIpcCloseMemHandle(p); link->opened.clear(); }
     if (h->d_flags) cudaFree(h->d_flags);
+    if (h->d_sync) cudaFree(h->d_sync);
     if (h->h_timeout) cudaFreeHost(const_cast<unsigned long long*>(h->h_timeout));
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     if (h->ev_bnd) cudaEventDestroy(h->ev_bnd);
@@ -1511,13 +1701,19 @@ int fdtd_b200_step_path(fdtd_b200_handle h, char* buf, size_t cap) {
     const std::string arith = mode == 0 ? "fast" : (mode == 1 ? "exact" : "exact-div");
     const std::string idx = h->idx_bytes == 1 ? "u8" : "u16";
     std::string s;
+    if (h->resident < 0) resident_decide(h);
+    if (h->resident > 0) {
+        s = "resident: k_steps_resident<" + arith + "," + idx + "> — " + std::to_string(h->n_local) + " cells held in registers / L2, n steps per launch, " +
+            (h->resident == 1 ? "one cluster of " : "cooperative grid of ") + std::to_string(h->resident_ctas) + " CTAs x 512 threads x " + std::to_string(h->resident_cpt) + " cells; plane-range / slab calls use: ";
+    }
+    else if (!h->resident_why_not.empty() && h->n_local <= (1u << 22)) s = "[not resident: " + h->resident_why_not + "] ";
     if (h->fused) {
-        s = "fused: k_step_fused<" + arith + "," + idx + ">";
+        s += "fused: k_step_fused<" + arith + "," + idx + ">";
         if (h->nx != h->nxl) s += " xpad";
         if (h->has_pml) s += h->pml_in_kernel ? " + CPML inside the kernel" : " + CPML passes (x slabs do not fit the in-kernel tiling, or FDTD_B200_PML_PASSES=1)";
         if (h->p2p) s += " + peer-memory halos";
     } else {
-        s = std::string("two-kernel (") + (use_bulk(h) ? "bulk" : (h->vec4 ? "vec4" : "generic")) + "): k_update_{h,e}_" +
+        s += std::string("two-kernel (") + (use_bulk(h) ? "bulk" : (h->vec4 ? "vec4" : "generic")) + "): k_update_{h,e}_" +
             (use_bulk(h) ? "bulk" : (h->vec4 ? "vec4" : "generic")) + "<" + arith + "," + idx + ">; not fused: " + h->fused_why_not;
         if (h->has_pml) s += " + CPML passes";
     }
@@ -1761,6 +1957,12 @@ int fdtd_b200_step(fdtd_b200_handle h, uint64_t n_steps) {
     if (int rc = set_device(h)) return rc;
     const int nzl = static_cast<int>(h->nzl);
     const HostRowScope scope(h, n_steps == 1);
+    if (n_steps > 0 && resident_now(h)) {
+        const int rc = step_resident(h, n_steps);
+        if (rc == FDTD_B200_OK) return (n_steps == 1 && h->n_probes_total) ? probe_mirror_row(h, h->tick - 1) : FDTD_B200_OK;
+        if (rc > 0) return rc;
+        // rc < 0: the resident launch was refused before anything ran; h->resident is now 0 and the regular kernels take over
+    }
     for (uint64_t s = 0; s < n_steps; ++s) {
         if (h->fused) {
             if (int rc = launch_fused(h, 0, nzl)) return rc;
@@ -1931,6 +2133,7 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
     h->row_in_host.clear();
     if (h->d_probe_ring) { cudaFree(h->d_probe_ring); h->d_probe_ring = nullptr; }
     h->n_probes_total = 0; h->n_probes_local = 0;
+    h->probe_cells_host.clear();
     h->probe_first_tick = h->tick;
     probe_mirror_invalidate(h);
     if (n == 0) return FDTD_B200_OK;
@@ -1972,6 +2175,7 @@ int fdtd_b200_register_probes(fdtd_b200_handle h, uint32_t n, const uint64_t* ce
         CU_TRY(h, cudaMemcpy(h->d_probe_cells, lc.data(), sizeof(long long) * lc.size(), cudaMemcpyHostToDevice));
         CU_TRY(h, cudaMemcpy(h->d_probe_slot, slot.data(), sizeof(int) * slot.size(), cudaMemcpyHostToDevice));
         h->n_probes_local = static_cast<uint32_t>(loc.size());
+        h->probe_cells_host = lc;
     }
     return FDTD_B200_OK;
 }
@@ -1987,7 +2191,14 @@ int fdtd_b200_read_probes(fdtd_b200_handle h, uint64_t first_tick, uint64_t n_st
     const int pslot = static_cast<int>(first_tick % fdtd_b200_solver::PIN_SLOTS);
     if (n_steps == 1 && (h->pin_probe || h->h_probe_ring) && h->pin_probe_ev[pslot] && h->pin_probe_tick[pslot] == first_tick + 1) {
         // the row reached pinned memory behind its step: wait for that alone — later steps may be in flight
-        CU_TRY(h, cudaEventSynchronize(h->pin_probe_ev[pslot]));
+        // spin on the event for a while before blocking: on lattices whose step takes a few µs the wake-up latency of
+        // cudaEventSynchronize (≈ 10 µs) would be most of the per-step protocol's time
+        {
+            cudaError_t q = cudaErrorNotReady;
+            for (int spin = 0; spin < 20000 && q == cudaErrorNotReady; ++spin) q = cudaEventQuery(h->pin_probe_ev[pslot]);
+            if (q == cudaErrorNotReady) { (void)cudaGetLastError(); q = cudaEventSynchronize(h->pin_probe_ev[pslot]); }
+            CU_TRY(h, q);
+        }
         const bool in_host = h->h_probe_ring && h->row_in_host[first_tick % h->ring_steps];
         const float* src = in_host ? h->h_probe_ring + (first_tick % h->ring_steps) * row : h->pin_probe + pslot * h->pin_probe_floats;
         std::memcpy(out, src, row * sizeof(float));
