@@ -345,12 +345,12 @@ int pick_shape(fdtd_b200_handle h) {
 
 int pick_zc(fdtd_b200_handle h, int planes) {
     if (h->tune.zc > 0) return h->tune.zc;
-    // enough CTAs for several waves over 148 SMs, but long enough marches that the extra
+    // enough CTAs for several waves over the device's SMs (148 on a B200), but long enough marches that the extra
     // z∓1 prologue plane (2 of 9 streams) stays a small fraction of the traffic
     const Shape sh = kShapes[pick_shape(h)];
     const long long row_blocks = ((static_cast<long long>(h->nx) / 4 + sh.bx - 1) / sh.bx) * ((static_cast<long long>(h->ny) + sh.by - 1) / sh.by);
     int zc = 16;
-    while (zc > 4 && row_blocks * ((planes + zc - 1) / zc) < 148LL * 16) zc >>= 1;
+    while (zc > 4 && row_blocks * ((planes + zc - 1) / zc) < static_cast<long long>(h->n_sm) * 16) zc >>= 1;
     return zc;
 }
 
@@ -430,7 +430,7 @@ int launch_bulk(fdtd_b200_handle h, bool e_step, int z_lo, int z_hi) {
         // long marches amortise the ring's fill latency; keep >= ~3 waves of CTAs over the 148 SMs
         const long long tiles = static_cast<long long>((L.nx + 4 * BX - 1) / (4 * BX)) * ((L.ny + BY - 1) / BY);
         zc = 64;
-        while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < 148LL * 2 * 3) zc >>= 1;
+        while (zc > 8 && tiles * ((z_hi - z_lo + zc - 1) / zc) < static_cast<long long>(h->n_sm) * 2 * 3) zc >>= 1;
     }
     dim3 block(BX, BY, 1);
     dim3 grid((L.nx + 4 * BX - 1) / (4 * BX), (L.ny + BY - 1) / BY, (z_hi - z_lo + zc - 1) / zc);
@@ -1218,6 +1218,7 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
     } while (0)
 
     CU_NEW(cudaSetDevice(h->device));
+    if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
     CU_NEW(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
 

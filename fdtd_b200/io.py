@@ -208,18 +208,22 @@ class PngSequence:
 
 
 # ---- checkpoints ------------------------------------------------------------------------------------------------------------
-_MAGIC = b"FDTDB200CKPT\x01\x00\x00\x00"
+_MAGIC_V1 = b"FDTDB200CKPT\x01\x00\x00\x00"
+_MAGIC = b"FDTDB200CKPT\x02\x00\x00\x00"
+_HEADER = "<6QQdQ"   # nx ny nz z_begin z_end n_psi | tick | time | row pitch of the ψ blob
 
 
 def save_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
-    """Header + E planes + H planes ([z][y][x][3] f32) of this handle's slab, streamed `planes_per_chunk` at a time."""
+    """Header + E planes + H planes ([z][y][x][3] f32, the caller's nx-wide lattice) of this handle's slab, streamed
+    `planes_per_chunk` at a time, then the CPML ψ state.  The ψ blob is the handle's own (row-pitched) layout, so the header
+    records the pitch and `load_checkpoint` refuses a handle that stores its rows differently."""
     nx, ny, _ = state.lattice
     zb, ze = state.z_begin, state.z_end
     state.sync()
     tmp = path + ".tmp"
     with open(tmp, "wb") as f:
         psi = state.read_pml_state()   # CPML ψ arrays (empty without a PML)
-        f.write(_MAGIC + struct.pack("<6QQd", nx, ny, state.lattice[2], zb, ze, psi.size, state.tick(), state.time()))
+        f.write(_MAGIC + struct.pack(_HEADER, nx, ny, state.lattice[2], zb, ze, psi.size, state.tick(), state.time(), state.row_pitch))
         for comp in (FieldComponent.E, FieldComponent.H):
             for z in range(zb, ze, planes_per_chunk):
                 z1 = min(z + planes_per_chunk, ze)
@@ -230,14 +234,31 @@ def save_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
 
 def load_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
     """Restores fields, tick and time into a state created for the same lattice/slab (materials, PML profiles, sources and probes
-    belong to the instance and are not part of the checkpoint; the PML's ψ state is).  Slab-decomposed runs refresh their halos afterwards."""
+    belong to the instance and are not part of the checkpoint; the PML's ψ state is).  Everything that can be wrong with the file
+    — magic, lattice, slab, ψ count, ψ row pitch, length — is checked BEFORE the first byte is written into the state, so a
+    mismatch or a truncated file leaves the state as it was.  Slab-decomposed runs refresh their halos afterwards."""
     nx, ny, nz = state.lattice
+    size = os.path.getsize(path)
     with open(path, "rb") as f:
-        if f.read(len(_MAGIC)) != _MAGIC:
+        magic = f.read(len(_MAGIC))
+        if magic not in (_MAGIC, _MAGIC_V1):
             raise ValueError(f"{path}: not a fdtd_b200 checkpoint")
-        hx, hy, hz, zb, ze, n_psi, tick, time = struct.unpack("<6QQd", f.read(64))
+        if magic == _MAGIC:
+            hx, hy, hz, zb, ze, n_psi, tick, time, pitch = struct.unpack(_HEADER, f.read(struct.calcsize(_HEADER)))
+        else:   # version 1 had no pitch field: its ψ blob is only valid for a handle with unpadded rows
+            hx, hy, hz, zb, ze, n_psi, tick, time = struct.unpack("<6QQd", f.read(64))
+            pitch = hx
         if (hx, hy, hz, zb, ze) != (nx, ny, nz, state.z_begin, state.z_end):
             raise ValueError(f"{path}: checkpoint of lattice {(hx, hy, hz)} slab {(zb, ze)} does not match this state")
+        have_psi = state.read_pml_state().size
+        if n_psi != have_psi:
+            raise ValueError(f"{path}: checkpoint carries {n_psi} ψ values, this state's PML has {have_psi}")
+        if n_psi and pitch != state.row_pitch:
+            raise ValueError(f"{path}: the ψ state was saved with rows of {pitch} cells, this handle stores rows of {state.row_pitch} "
+                             "(row padding / FDTD_B200_NO_ROW_PADDING / forced generic kernels differ between the two handles)")
+        body = 2 * 3 * 4 * nx * ny * (ze - zb) + 4 * n_psi
+        if size != f.tell() + body:
+            raise ValueError(f"{path}: truncated or oversized checkpoint ({size} bytes, expected {f.tell() + body})")
         for comp in (FieldComponent.E, FieldComponent.H):
             for z in range(zb, ze, planes_per_chunk):
                 z1 = min(z + planes_per_chunk, ze)
@@ -246,8 +267,6 @@ def load_checkpoint(state, path: str, planes_per_chunk: int = 16) -> None:
                 if buf.size != n:
                     raise ValueError(f"{path}: truncated checkpoint")
                 state.write_field(comp, buf, (0, 0, z), (nx, ny, z1))
-        if n_psi != state.read_pml_state().size:
-            raise ValueError(f"{path}: checkpoint carries {n_psi} ψ values, this state's PML has {state.read_pml_state().size}")
         if n_psi:
             state.write_pml_state(np.frombuffer(f.read(4 * n_psi), dtype=np.float32))
     state.set_time(int(tick), float(time))

@@ -211,6 +211,11 @@ class PmlProfiles:
         """`thickness` PML cells on both faces of each axis, graded with `PmlCoefficients::new_graded` over the normalised
         depth.  On this lattice H[i] sits half a cell below E[i] (backward differences, cpu/mod.rs:431-443), so with
         `staggered` the H profile is evaluated at i − ½; staggered=False is the reference's one-set-per-cell model."""
+        if pml.kappa_max != 1.0:
+            # κ enters b and c exactly as in pml.rs:34-86, but a coordinate stretch also divides the curl's derivative by κ,
+            # which neither the reference's update (cpu/mod.rs:460-461, 502-503) nor this engine's does: refuse instead of
+            # silently running a different PML than the one asked for
+            raise ValueError("GradedPml.kappa_max != 1 is not supported: the update has no 1/kappa stretch on the curl")
         n = config.lattice_size()
         out = PmlProfiles(n)
         for a in axes:

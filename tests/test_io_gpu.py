@@ -73,3 +73,53 @@ def test_checkpoint_resume_is_bit_exact(b200, tmp_path, fused):
                                                    _random_workload(b200, (128, 12, 9), seed=9).domain()).create_state()
     with pytest.raises(ValueError):
         fio.load_checkpoint(other, path)
+
+
+def test_bad_checkpoints_leave_the_state_untouched(b200, tmp_path, monkeypatch):
+    """Everything wrong with a checkpoint file is found before the first byte reaches the state: a truncated file, a ψ count
+    that does not match the handle's PML and a ψ blob saved with another row pitch all raise and change nothing."""
+    from fdtd_b200 import io as fio
+
+    size = (100, 12, 10)                                   # rows padded to 128 cells
+    w = _random_workload(b200, size, seed=4)
+    w.pml = b200.PmlProfiles.graded(w.solver_config(), 3)
+
+    def fresh(with_pml=True):
+        ww = _random_workload(b200, size, seed=4)
+        ww.pml = w.pml if with_pml else None
+        return b200.FdtdB200Backend(exact_arithmetic=True).create_instance(ww.solver_config(), ww.domain()).create_state()
+
+    a = fresh()
+    a.set_source_table(w.source_points(), w.source_table(5))
+    a.step(5)
+    path = str(tmp_path / "ck.bin")
+    fio.save_checkpoint(a, path)
+    blob = open(path, "rb").read()
+
+    b = fresh()
+    b.set_source_table(w.source_points(), w.source_table(2))
+    b.step(2)
+    before = (b.read_field(b200.FieldComponent.E).copy(), b.read_field(b200.FieldComponent.H).copy(), b.tick(), b.time())
+
+    def unchanged():
+        return (np.array_equal(b.read_field(b200.FieldComponent.E), before[0]) and np.array_equal(b.read_field(b200.FieldComponent.H), before[1])
+                and b.tick() == before[2] and b.time() == before[3])
+
+    cut = str(tmp_path / "cut.bin")
+    open(cut, "wb").write(blob[: len(blob) - 100])
+    with pytest.raises(ValueError, match="truncated"):
+        fio.load_checkpoint(b, cut)
+    assert unchanged()
+    nopml = fresh(with_pml=False)
+    with pytest.raises(ValueError, match="ψ values"):
+        fio.load_checkpoint(nopml, path)
+    assert nopml.tick() == 0 and not np.any(nopml.read_field(b200.FieldComponent.E))
+    monkeypatch.setenv("FDTD_B200_NO_ROW_PADDING", "1")
+    c = fresh()
+    assert c.row_pitch == 100 and a.row_pitch == 128
+    with pytest.raises(ValueError, match="ψ values|rows of 128 cells"):      # the ψ arrays of a padded handle are larger, which is caught first
+        fio.load_checkpoint(c, path)
+    assert c.tick() == 0 and not np.any(c.read_field(b200.FieldComponent.H))
+    monkeypatch.delenv("FDTD_B200_NO_ROW_PADDING")
+    fio.load_checkpoint(b, path)                           # and the good file still loads
+    assert b.tick() == 5 and np.array_equal(b.read_field(b200.FieldComponent.E), a.read_field(b200.FieldComponent.E))

@@ -200,3 +200,11 @@ def test_scene_pml_region_that_is_not_a_slab_is_refused(b200):
     sc, _, _, _ = _pml_scene(b200, half=(0.04, 0.02, 0.5))                                # does not span the lattice in y
     with pytest.raises(ValueError):
         sc.pml_profiles
+
+
+def test_kappa_stretch_is_refused_not_silently_dropped(b200):
+    """κ_max ≠ 1 would need the curl's derivative divided by κ, which neither the reference's update nor this engine has."""
+    cfg = b200.FdtdSolverConfig.from_lattice((32, 16, 8), b200.Resolution((1, 1, 1), 0.25), b200.PhysicalConstants.REDUCED)
+    with pytest.raises(ValueError, match="kappa"):
+        b200.PmlProfiles.graded(cfg, 4, b200.GradedPml(kappa_max=2.0))
+    assert b200.PmlProfiles.graded(cfg, 4, b200.GradedPml(kappa_max=1.0)).any()
