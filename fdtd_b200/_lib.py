@@ -21,6 +21,7 @@ COLORMAP_CPU, COLORMAP_LINEAR, COLORMAP_APP_Z = 0, 1, 2
  HALO_SEND_MAT_BOTTOM, HALO_RECV_MAT_HIGH) = range(16)
 HALO_PENDING = 0x100
 P2P_BLOB_BYTES = 2048
+STATIC_SCRATCH_BYTES = 8 << 20   # fdtd_b200_read_field_static: at most STATIC_SCRATCH_BYTES // 12 cells per call
 
 
 class Material(C.Structure):
@@ -126,6 +127,7 @@ SYMBOLS = {
     "fdtd_b200_rasterize_scene": (C.c_int, [C.c_int, _u64p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32, _u32p]),
     "fdtd_b200_set_materials_from_scene": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(Shape), C.c_uint32, C.c_uint32]),
     "fdtd_b200_read_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
+    "fdtd_b200_read_field_static": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_write_field": (C.c_int, [_H, C.c_int, _u64p, _u64p, _fp]),
     "fdtd_b200_device_field": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p)]),
     "fdtd_b200_row_pitch": (C.c_uint64, [_H]),

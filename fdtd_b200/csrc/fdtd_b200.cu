@@ -2762,3 +2762,59 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
 }
 
 }  // extern "C"
+
+// ---- field readback without any allocation ---------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  fdtd_b200_read_field gathers the box into a
+// staging buffer that it (re)allocates on demand; this variant gathers into a file-scope device array of a fixed, modest size.
+// Every GPU that loads the library holds the array (FDTD_B200_STATIC_SCRATCH_BYTES) until the process exits.  All calls, on all
+// handles of a device, share it, and it keeps the last call's contents: the gather kernel overwrites every element it later copies
+// out, so nothing has to start at zero — but two calls that overlap on the GPU (different streams / threads) race on it.
+static __device__ __align__(256) float g_static_scratch[FDTD_B200_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the address the kernel needs comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+int static_scratch_ptr(fdtd_b200_handle h, float** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static float* ptr[kMaxDevices] = {};
+    if (h->device < 0 || h->device >= kMaxDevices) return fail(h, FDTD_B200_EINVAL, "device ordinal beyond the static scratch table");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[h->device]) {
+        void* p = nullptr;
+        CU_TRY(h, cudaGetSymbolAddress(&p, g_static_scratch));   // the caller made h->device current (set_device)
+        if (!p) return fail(h, FDTD_B200_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+        ptr[h->device] = static_cast<float*>(p);
+    }
+    *out = ptr[h->device];
+    return FDTD_B200_OK;
+}
+
+}  // namespace
+
+extern "C" int fdtd_b200_read_field_static(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out) {
+    if (!h) return fail(nullptr, FDTD_B200_EINVAL, "NULL handle");
+    if (component != FDTD_B200_FIELD_E && component != FDTD_B200_FIELD_H) return fail(h, FDTD_B200_EINVAL, "component must be E or H");
+    BoxView B{};
+    size_t n = 0;
+    if (int rc = make_box(h, lo, hi, &B, &n)) return rc;
+    if (n == 0) return FDTD_B200_OK;
+    if (!out) return fail(h, FDTD_B200_EINVAL, "NULL output buffer");
+    constexpr size_t kMaxCells = FDTD_B200_STATIC_SCRATCH_BYTES / (3 * sizeof(float));
+    if (n > kMaxCells)
+        return fail(h, FDTD_B200_EINVAL, "fdtd_b200_read_field_static: box of " + std::to_string(n) + " cells exceeds the static scratch array (" +
+                                             std::to_string(kMaxCells) + " cells = FDTD_B200_STATIC_SCRATCH_BYTES / 12); use fdtd_b200_read_field or read the box in parts");
+    if (int rc = set_device(h)) return rc;
+    float* scratch = nullptr;
+    if (int rc = static_scratch_ptr(h, &scratch)) return rc;
+    const int c0 = component == FDTD_B200_FIELD_E ? 0 : 3;
+    const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, static_cast<size_t>(h->n_sm) * 16));
+    k_gather_box<<<blocks, 256, 0, h->stream>>>(h->f[c0], h->f[c0 + 1], h->f[c0 + 2], B, scratch);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    CU_TRY(h, cudaMemcpyAsync(out, scratch, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return p2p_poisoned(h);
+}

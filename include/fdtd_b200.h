@@ -357,6 +357,16 @@ int fdtd_b200_set_materials_from_scene(fdtd_b200_handle h, const double solver_t
  * interleaved, x fastest — the fresh field (buffer tick%2, cpu/mod.rs:538).  The box must lie in
  * this handle's slab.  Blocks until the data is on the host. */
 int fdtd_b200_read_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out);
+/* The same readback for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * fdtd_b200_read_field gathers the box into a staging buffer it (re)allocates on demand; this variant gathers into a file-scope
+ * `static __device__` array of FDTD_B200_STATIC_SCRATCH_BYTES (8 MiB, held by every GPU that loads the library until the process
+ * exits) and calls no cudaMalloc / cudaFree / allocating routine.  Same arguments, same result, bit for bit.  Limit: the box may
+ * hold at most FDTD_B200_STATIC_SCRATCH_BYTES / 12 = 699 050 cells, else EINVAL (message names the limit) and nothing is read.
+ * All calls on a device share the one array, which keeps the previous call's contents (every element that is copied out is
+ * overwritten first, so nothing needs clearing): calls that overlap on the GPU — other threads, other handles' streams — race. */
+#define FDTD_B200_STATIC_SCRATCH_BYTES 8388608 /* 8 MiB */
+int fdtd_b200_read_field_static(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], float* out);
 /* The inverse (≙ FieldMut, lib.rs:114-127): overwrite a box of E or H. */
 int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3], const uint64_t hi[3], const float* in);
 /* Raw device pointer of one scalar component c in 0..5 = Ex,Ey,Ez,Hx,Hy,Hz (first owned plane).  Cell (x, y, z) of the

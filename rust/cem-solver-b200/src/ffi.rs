@@ -30,6 +30,7 @@ pub const FDTD_B200_SHAPE_CUBOID: u32 = 1;
 pub const FDTD_B200_SHAPE_CYLINDER: u32 = 2;
 
 pub const FDTD_B200_P2P_BLOB_BYTES: usize = 2048;
+pub const FDTD_B200_STATIC_SCRATCH_BYTES: usize = 8 << 20;
 
 /// Opaque `struct fdtd_b200_solver`; `fdtd_b200_handle` is a pointer to it.
 #[repr(C)]
@@ -313,6 +314,13 @@ unsafe extern "C" {
 
     // ---- field access
     pub fn fdtd_b200_read_field(
+        h: fdtd_b200_handle,
+        component: c_int,
+        lo: *const u64,
+        hi: *const u64,
+        out: *mut f32,
+    ) -> c_int;
+    pub fn fdtd_b200_read_field_static(
         h: fdtd_b200_handle,
         component: c_int,
         lo: *const u64,
