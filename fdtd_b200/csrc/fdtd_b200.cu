@@ -2565,11 +2565,10 @@ int p2p_push(fdtd_b200_handle h, int set, cudaStream_t st, bool stored_by_kernel
 
 int p2p_wait(fdtd_b200_handle h, cudaStream_t st) {
     if (h->halo_seq == 0) return FDTD_B200_OK;
-    static const long long max_cycles = [] {   // ≈ 10 s at 1.9 GHz; FDTD_B200_P2P_TIMEOUT_MS shortens it (tests)
-        const char* e = std::getenv("FDTD_B200_P2P_TIMEOUT_MS");
-        const long long ms = e ? std::atoll(e) : 0;
-        return (ms > 0 ? ms : 10000LL) * 1900000LL;
-    }();
+    // ≈ 10 s at 1.9 GHz; FDTD_B200_P2P_TIMEOUT_MS shortens it (read per call: tests set it for one case)
+    const char* e_ms = std::getenv("FDTD_B200_P2P_TIMEOUT_MS");
+    const long long ms_env = e_ms ? std::atoll(e_ms) : 0;
+    const long long max_cycles = (ms_env > 0 ? ms_env : 10000LL) * 1900000LL;
     if (h->lower.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 0, h->halo_seq, h->hd_timeout, max_cycles);
     if (h->upper.present) k_wait_flag<<<1, 1, 0, st>>>(h->d_flags + 1, h->halo_seq, h->hd_timeout, max_cycles);
     CU_TRY(h, cudaGetLastError());

@@ -253,3 +253,40 @@ def test_fused_step_with_large_coefficient_tables(b200, oracle, tune, n_material
     assert st.uses_fused
     assert np.array_equal(st.read_field(b200.FieldComponent.E), ref.field(oracle.E).astype(np.float32))
     assert np.array_equal(st.read_field(b200.FieldComponent.H), ref.field(oracle.H).astype(np.float32))
+
+
+def test_a_missing_neighbour_poisons_the_handle_instead_of_yielding_stale_fields(b200, tune, monkeypatch):
+    """a flag wait that gives up must be sticky and fatal.  Two slabs in one process; the lower one is
+    stepped twice while the upper one never takes its first step, so the lower slab's second boundary launch waits for a push
+    that does not come.  After the (shortened) timeout every entry point that steps, reads or writes state on that handle fails
+    with ECUDA — no fields or probe rows computed on stale ghost planes are handed out — and the healthy handle still works."""
+    from fdtd_b200 import _lib as L
+
+    tune(None)
+    monkeypatch.setenv("FDTD_B200_P2P_TIMEOUT_MS", "150")
+    w = _random_workload(b200, (128, 8, 8), seed=3)
+    probes = [(5, 1, 2)]
+    a = b200.FdtdB200Backend(z_slab=(0, 4)).create_instance(w.solver_config(), w.domain()).create_state()
+    b = b200.FdtdB200Backend(z_slab=(4, 8)).create_instance(w.solver_config(), w.domain()).create_state()
+    ba, bb = a.p2p_export(), b.p2p_export()
+    a.p2p_connect(None, bb)
+    b.p2p_connect(ba, None)
+    with pytest.raises(L.Fdtd_b200Error) as ei:
+        a.p2p_step(1)                                        # nothing pushed yet: stale ghost planes are refused up front
+    assert ei.value.code == L.ESTATE and "p2p_refresh" in str(ei.value)
+    for st in (a, b):
+        st.register_probes(probes)
+        st.p2p_refresh()
+    a.p2p_step(1)                                            # waits for b's refresh push: fine
+    a.sync()
+    with pytest.raises(L.Fdtd_b200Error) as ei:
+        a.p2p_step(4)                                        # several steps per call cannot work with both slabs on one host thread
+    assert ei.value.code == L.EINVAL
+    a.p2p_step(1)                                            # waits for b's push of step 1, which never comes
+    for call in (a.sync, lambda: a.read_field(b200.FieldComponent.E), lambda: a.read_probes(1, 1), lambda: a.p2p_step(1),
+                 a.p2p_refresh, lambda: a.write_field(b200.FieldComponent.E, np.zeros((4, 8, 128, 3), np.float32))):
+        with pytest.raises(L.Fdtd_b200Error) as ei:
+            call()
+        assert ei.value.code == L.ECUDA and "timed out waiting for a neighbour's halo flag" in str(ei.value)
+    b.sync()                                                 # the other handle is not affected
+    assert b.tick() == 0 and b.read_field(b200.FieldComponent.H).shape == (4, 8, 128, 3)
