@@ -21,6 +21,7 @@
 #include "kernels_scene.cuh"
 #include "kernels_pml.cuh"
 #include "kernels_resident.cuh"
+#include "kernels_2d.cuh"
 
 using namespace fdtd_b200;
 
@@ -72,6 +73,8 @@ struct fdtd_b200_solver {
     unsigned long long* d_sync = nullptr;      // grid-barrier slots of the resident kernel (one per CTA), epochs keep counting across launches
     unsigned long long sync_epoch = 0;
     int resident_ctas = 0, resident_cpt = 1;   // CTAs of the resident launch, cells per thread
+    int step2d = -1;                // -1 not decided | 0 no | 1 the y-marching fused kernel for nz == 1 (kernels_2d.cuh)
+    int step2d_slots = 0;           // CTAs of k_step_2d resident on the device at once (occupancy × SMs)
     int zc_override = 0;            // planes per CTA march forced for the next fused launches (fdtd_b200_p2p_step's chunk-aligned split)
     int n_sm = 0;                   // SMs of the device (queried at the first fused launch)
     int sm_smem_bytes = 0, sm_smem_reserved = 0;   // shared memory per SM / reserved per CTA (queried at the first fused launch)
@@ -880,12 +883,66 @@ void prof_clear(fdtd_b200_handle h) {
     }
 }
 
+// ---- two-dimensional lattices: the y-marching fused kernel (kernels_2d.cuh) ---------------------------------------------------
+bool step2d_now(fdtd_b200_handle h) {
+    if (h->step2d < 0) {
+        h->step2d = 0;
+        const char* e = std::getenv("FDTD_B200_STEP2D");
+        if (h->fused && h->nz == 1 && h->ny >= 2 && h->tune.zc <= 0 && h->tune.variant < 0 && !(e && e[0] == '0')) h->step2d = 1;
+    }
+    return h->step2d == 1 && !h->has_pml;
+}
+
+template <int EXACT, typename IdxT>
+int launch_2d_t(fdtd_b200_handle h) {
+    auto k = k_step_2d<EXACT, IdxT>;
+    const int table_in_smem = h->n_table <= static_cast<uint32_t>(k2dTableMax) ? 1 : 0;
+    const int smem = k2d_smem_bytes(table_in_smem ? static_cast<int>(h->n_table) : 0);
+    if (h->step2d_slots == 0) {
+        int per_sm = 0;
+        if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, 32 * k2dWarps, smem) != cudaSuccess || per_sm <= 0) { (void)cudaGetLastError(); per_sm = 4; }
+        h->step2d_slots = per_sm * h->n_sm;
+    }
+    Step2dView V{};
+    for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
+    V.mat = h->mat; V.table = h->table; V.n_table = static_cast<int>(h->n_table); V.table_in_smem = table_in_smem;
+    V.nx = static_cast<int>(h->nx); V.ny = static_cast<int>(h->ny); V.nxl = static_cast<int>(h->nxl);
+    for (int a = 0; a < 3; ++a) { V.dx[a] = static_cast<float>(h->cfg.dx[a]); V.inv_dx[a] = 1.0f / V.dx[a]; }
+    const int n_xseg = (V.nx / 4 + k2dOwned - 1) / k2dOwned;
+    // Rows per march: 8, measured.  A cost model like pick_fused_zc's (longer marches amortise the two extra rows, one full wave
+    // beats 3.1 waves) predicts 48 rows for 4096×4096 — and is wrong: 4096×4096×1 runs at 122.5 Gcells/s with 8-row marches, 115 with
+    // 12–16, 108 with 32, 100 with 48, 113 with 4 (profiles/r02_exp_2d_kernel.txt), with a 3- or a 4-slot ring alike.  Warps that
+    // march independently for long drift apart and their concurrent accesses lose DRAM-page / L2 locality; short marches re-align
+    // them every few rows, and the rows re-read at the seams (2 of 8) come from L2.  Lattices too small to fill the device's warp
+    // slots with 8-row items take 6- or 4-row marches.
+    const double warp_slots = static_cast<double>(h->step2d_slots) * k2dWarps;
+    int yc = std::min(V.ny, 8);
+    while (yc > 4 && static_cast<double>(n_xseg) * ((V.ny + yc - 1) / yc) < warp_slots) yc -= 2;
+    if (const char* e = std::getenv("FDTD_B200_STEP2D_YC")) if (std::atoi(e) > 0) yc = std::atoi(e);
+    const int items = n_xseg * ((V.ny + yc - 1) / yc);
+    dim3 grid((items + k2dWarps - 1) / k2dWarps, 1, 1);
+    k<<<grid, 32 * k2dWarps, smem, h->stream>>>(V, forcing_view(h), probe_view(h), yc);
+    h->launches += 1;
+    CU_TRY(h, cudaGetLastError());
+    return FDTD_B200_OK;
+}
+
+int launch_2d(fdtd_b200_handle h, int mode) {
+    if (h->idx_bytes == 1) return mode == 0 ? launch_2d_t<0, uint8_t>(h) : (mode == 1 ? launch_2d_t<1, uint8_t>(h) : launch_2d_t<2, uint8_t>(h));
+    return mode == 0 ? launch_2d_t<0, uint16_t>(h) : (mode == 1 ? launch_2d_t<1, uint16_t>(h) : launch_2d_t<2, uint16_t>(h));
+}
+
 // planes [z_lo, z_hi) of the current set → the pending set (no swap)
 int launch_fused(fdtd_b200_handle h, int z_lo, int z_hi, bool push = false) {
     if (z_lo >= z_hi) return FDTD_B200_OK;
     const int mode = arithmetic_mode(h);
     if (int rc = prof_begin(h, 0, z_hi - z_lo)) return rc;
     int rc;
+    if (!push && z_lo == 0 && z_hi == 1 && h->nzl == 1 && step2d_now(h)) {
+        if ((rc = launch_2d(h, mode))) return rc;
+        return prof_end(h, 0);
+    }
     const bool whole = z_lo == 0 && z_hi == static_cast<int>(h->nzl) && h->z_begin == 0 && h->z_end == h->nz;
     const bool pml = h->has_pml && h->pml_in_kernel;
     if (h->has_pml && !pml && !whole)
@@ -1704,11 +1761,15 @@ int fdtd_b200_step_path(fdtd_b200_handle h, char* buf, size_t cap) {
     std::string s;
     if (h->resident < 0) resident_decide(h);
     if (h->resident > 0) {
-        s = "resident: k_steps_resident<" + arith + "," + idx + "> — " + std::to_string(h->n_local) + " cells held in registers / L2, n steps per launch, " +
+        s = std::string("resident: ") + (h->resident == 1 ? "k_steps_cluster<" : "k_steps_resident<") + arith + "," + idx + "> — " + std::to_string(h->n_local) +
+            (h->resident == 1 ? " cells held in registers / distributed shared memory, n steps per launch, " : " cells held in registers / L2, n steps per launch, ") +
             (h->resident == 1 ? "one cluster of " : "cooperative grid of ") + std::to_string(h->resident_ctas) + " CTAs x 512 threads x " + std::to_string(h->resident_cpt) + " cells; plane-range / slab calls use: ";
     }
     else if (!h->resident_why_not.empty() && h->n_local <= (1u << 22)) s = "[not resident: " + h->resident_why_not + "] ";
-    if (h->fused) {
+    if (h->fused && step2d_now(h)) {
+        s += "fused 2-D: k_step_2d<" + arith + "," + idx + "> (nz == 1: y-marching single pass, warp-shuffle x neighbours)";
+        if (h->nx != h->nxl) s += " xpad";
+    } else if (h->fused) {
         s += "fused: k_step_fused<" + arith + "," + idx + ">";
         if (h->nx != h->nxl) s += " xpad";
         if (h->has_pml) s += h->pml_in_kernel ? " + CPML inside the kernel" : " + CPML passes (x slabs do not fit the in-kernel tiling, or FDTD_B200_PML_PASSES=1)";

@@ -55,7 +55,8 @@ def test_resident_exact_mode_is_bit_identical_to_f32_oracle(b200, oracle, reside
     steps = 12
     ref, s32 = oracle_run(oracle, w, steps, oracle.F32, init=init, probes=probes)
     _, st, series = b200_run(b200, w, steps, exact=True, init=init, probes=probes, fused=None)
-    assert st.step_path.startswith("resident: k_steps_resident<exact,u8>") and ("one cluster" if kind == "cluster" else "cooperative grid") in st.step_path, st.step_path
+    kernel = "k_steps_cluster" if kind == "cluster" else "k_steps_resident"
+    assert st.step_path.startswith(f"resident: {kernel}<exact,u8>") and ("one cluster" if kind == "cluster" else "cooperative grid") in st.step_path, st.step_path
     assert st.kernel_launches <= 6, "n steps are one launch"       # + the uploads' helper kernels
     e, h = _fields(st, b200)
     assert st.tick() == steps == ref.tick and st.time() == ref.time
@@ -98,7 +99,7 @@ def test_resident_u16_index_true_division_and_batched_vs_per_step(b200, oracle, 
     steps = 9
     ref, s32 = oracle_run(oracle, w, steps, oracle.F32, init=init, probes=probes)
     _, st, series = b200_run(b200, w, steps, exact=True, init=init, probes=probes, fused=None)
-    assert "k_steps_resident<exact-div,u16>" in st.step_path
+    assert st.step_path.startswith("resident: k_steps_") and "<exact-div,u16>" in st.step_path, st.step_path
     e, h = _fields(st, b200)
     assert np.array_equal(e, ref.field(oracle.E).astype(np.float32)) and np.array_equal(h, ref.field(oracle.H).astype(np.float32))
     assert np.array_equal(series, s32.astype(np.float32))
