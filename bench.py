@@ -396,7 +396,7 @@ def run_b200(args) -> None:
     if args.pml:
         if world > 1 and (args.no_fused or args.transport != "p2p"):
             raise SystemExit("--pml on several GPUs runs inside the fused kernel over the peer-memory transport (drop --no-fused / --transport nccl)")
-        w.pml = fdtd_b200.PmlProfiles.graded(w.solver_config(), args.pml)
+        w.pml = fdtd_b200.PmlProfiles.graded(w.solver_config(), args.pml, axes=tuple("xyz".index(a) for a in args.pml_axes))
     # the default backend: whatever a caller of the reference-facing API gets (the fused step wherever eligible)
     backend = fdtd_b200.FdtdB200Backend(device=local_rank, exact_arithmetic=args.exact, z_slab=(z_begin, z_end) if world > 1 else None,
                                         fused_step=False if args.no_fused else None)
@@ -681,6 +681,7 @@ def main() -> None:
     ap.add_argument("--no-fused", action="store_true", help="two-kernel path (in-place, 24 B/cell of field memory) instead of the fused step")
     ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
                     help="weak: 512^3 cells per GPU (default, the driver's scaling run); strong: one fixed lattice (1024^3 unless --lattice) for every N")
+    ap.add_argument("--pml-axes", default="xyz", help="axes that carry the --pml slabs (experiments: x, y, z, xy, ...)")
     ap.add_argument("--pml", type=int, default=0, help="add CPML slabs of this many cells on all six faces (not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-slab-parity", action="store_true", help="skip the N>1 slab-parity self-check before the timed region")

@@ -162,6 +162,8 @@ struct fdtd_b200_solver {
     float* psi_ghost = nullptr;
     size_t ghost_plane[3] = {0, 0, 0};
     bool has_pml = false;
+    int heavy_key[3] = {-1, -1, -1};   // (z_lo, z_hi, zc) the cached dispatch order below was computed for; reset by pml_refresh_mode
+    int heavy_val[2][2] = {{0, 0}, {0, 0}};   // FusedPmlView::heavy of the y and z block indices
     bool pml_in_kernel = false;        // the fused kernel's PML instantiation runs the recursion (else: passes over the slabs)
 
     // NVLink peer-memory halo transport (fdtd_b200_p2p_*)
@@ -542,15 +544,16 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
 // partly idle for ≈ 0.43 of a march: cost(zc) = (ceil(tiles · chunks / slots) + 0.43) · (zc + c) with balanced chunks.
 // c and 0.43 are fitted to tools/exp_zc_midsize.sh (profiles/r01_exp_zc_midsize.txt: 256³ best at 16 planes, 384³ at 24,
 // 512³ at 32..64, 128 slower than the model says); the previous rule (halve 64 until 3 waves exist) left 384³ at 64 planes, 10 % slower.
-int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunks = 1) {
+int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunks = 1, int max_zc = 64) {
     if (h->n_sm == 0) {
         if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
     }
     const double slots = 2.0 * h->n_sm;
     static const int cand[] = {1, 2, 4, 6, 8, 12, 16, 20, 24, 28, 32, 40, 48, 56, 64};   // longer marches measured slower (128 planes: -6 %, profiles/r01_exp_plane_shape.txt)
-    int best = std::max(1, std::min(planes, 64));
+    int best = std::max(1, std::min(planes, max_zc));
     double best_cost = 1e300;
     for (int zc : cand) {
+        if (zc > max_zc) break;
         if (zc > planes && zc != cand[0]) { if (best_cost < 1e300) break; }
         const int chunks = (planes + zc - 1) / zc;
         if (chunks < min_chunks) continue;                // the peer-memory split wants a chunk per boundary plus an interior
@@ -614,7 +617,11 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     int zc = h->zc_override > 0 ? h->zc_override : h->tune.zc;
     if (zc <= 0) {
         const long long tiles = static_cast<long long>((V.nx + 4 * BX - 1) / (4 * BX)) * ((V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS);
-        zc = pick_fused_zc(h, tiles, z_hi - z_lo);
+        // The PML instantiation marches at most 32 planes: its CTAs differ in cost (x-slab tile columns +30 %, y-slab rows and
+        // z-slab planes more), neighbouring tiles drift apart over a long march and their shared halo rows fall out of L2 —
+        // DRAM reads per launch at 512³, 16-cell layers: 3.84 GB with 16-plane marches, 3.96 with 24, 4.13 with 32, 4.50 with 48,
+        // 4.76 with 64 (3.79 algorithmic); time: 1.446 / 1.399 / 1.397 / 1.413 / 1.517 ms (profiles/r02_exp_pml.txt).
+        zc = pick_fused_zc(h, tiles, z_hi - z_lo, 1, pml ? 32 : 64);
     }
     FusedPmlView Q{};
     if (pml) {
@@ -641,6 +648,24 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     }
     dim3 block(BX, BY, 1);
     dim3 grid((V.nx + 4 * BX - 1) / (4 * BX), (V.ny + LO::CORE_ROWS - 1) / LO::CORE_ROWS, (z_hi - z_lo + zc - 1) / zc);
+    if (pml) {
+        // slab tile rows and slab chunks first (FusedPmlView::heavy): the leading and the trailing run of blocks that hold a slab coordinate
+        auto runs = [](const std::vector<int>& pos, int origin, int extent, int count, int out[2]) {
+            std::vector<char> hit(static_cast<size_t>(count), 0);
+            for (int c : pos) { const int b = (c - origin) / extent; if (c >= origin && b < count) hit[static_cast<size_t>(b)] = 1; }
+            int p = 0, s = count;
+            while (p < count && hit[static_cast<size_t>(p)]) ++p;
+            while (s > p && hit[static_cast<size_t>(s - 1)]) --s;
+            out[0] = p; out[1] = s;
+        };
+        if (h->heavy_key[0] != z_lo || h->heavy_key[1] != z_hi || h->heavy_key[2] != zc) {   // once per launch shape, not per step
+            runs(h->pml[1].pos, 0, LO::CORE_ROWS, static_cast<int>(grid.y), h->heavy_val[0]);
+            runs(h->pml[2].pos, z_lo, zc, static_cast<int>(grid.z), h->heavy_val[1]);
+            h->heavy_key[0] = z_lo; h->heavy_key[1] = z_hi; h->heavy_key[2] = zc;
+        }
+        Q.heavy[0][0] = 0; Q.heavy[0][1] = static_cast<int>(grid.x);
+        for (int i = 0; i < 2; ++i) { Q.heavy[1][i] = h->heavy_val[0][i]; Q.heavy[2][i] = h->heavy_val[1][i]; }
+    }
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0, pml);
     const bool xpad = h->nxl != h->nx;
     auto k = pml ? (xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, true, true> : k_step_fused<EXACT, IdxT, BX, BY, false, true, false>)
@@ -669,12 +694,15 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
 void pml_refresh_mode(fdtd_b200_handle h) {
     h->resident = -1;   // a CPML changes whether the L2-resident multi-step kernel may run (decided again at the next step)
     h->pml_in_kernel = false;
+    h->heavy_key[0] = h->heavy_key[1] = h->heavy_key[2] = -1;
     if (!h->has_pml || !h->fused) return;
     if (const char* e = std::getenv("FDTD_B200_PML_PASSES")) if (e[0] == '1') return;
     for (int a = 0; a < 3; ++a) {
         if (h->pml[a].n && (!h->pml[a].d_map || !h->pml[a].psi_alt[0] || !h->pml[a].psi_alt[1])) return;
         if (h->pml[a].ghost && !h->pml[a].d_map) return;
     }
+    // the kernel indexes the x-slab arrays [z][y][k] with 32 bits (one more plane: the ghost above a z-slab)
+    if (static_cast<unsigned long long>(h->pml[0].n) * h->ny * (static_cast<unsigned long long>(h->nzl) + 1) >= (1ull << 31)) return;
     std::vector<int> per_tile(static_cast<size_t>(h->nx / 128 + 1), 0);
     for (int x : h->pml[0].pos)
         if (++per_tile[static_cast<size_t>(x / 128)] > 32) return;
@@ -2774,7 +2802,7 @@ int fdtd_b200_p2p_step(fdtd_b200_handle h, uint64_t n_steps) {
         constexpr int BX = 32, BYc = 7;   // tile of k_step_fused<…, 32, 8>: 128 cells × 7 core rows
         const long long tiles = static_cast<long long>((h->nx + 4 * BX - 1) / (4 * BX)) * ((h->ny + BYc - 1) / BYc);
         const int n_bnd = (h->lower.present ? 1 : 0) + (h->upper.present ? 1 : 0);
-        const int zc_full = h->tune.zc > 0 ? h->tune.zc : pick_fused_zc(h, tiles, n, n_bnd + 1);
+        const int zc_full = h->tune.zc > 0 ? h->tune.zc : pick_fused_zc(h, tiles, n, n_bnd + 1, h->has_pml ? 32 : 64);   // PML launches: see launch_fused_t
         if (zc_full * n_bnd < n) zc_chunk = zc_full;
     }
     const bool split = n >= 3;                      // otherwise the whole slab is "boundary"

@@ -79,8 +79,9 @@ struct FusedView {
 // CPML inside the fused step (template flag PML; SURVEY §8 f-2, formulas of kernels_pml.cuh).  The ψ recursion of an axis
 // uses the very derivatives the curl needs, so the slabs cost their ψ traffic only.  ψ_H is read by the recomputed halo
 // cells as well, so like the fields it is ping-pong buffered (gh_in → gh_out, written by the owner); ψ_E is touched by the
-// owner of E' alone and advanced in place.  y and z slabs are x-contiguous (one float4 per quad and array); the ψ of the
-// few x-slab cells of a tile row is staged into shared memory by 4-byte cp.async copies issued before the TMA wait.
+// owner of E' alone and advanced in place.  y and z slabs are x-contiguous (one float4 per quad and array); the few x-slab
+// cells of a tile row are advanced one per lane (lane j: the row's j-th x-slab cell; its ψ is loaded before the phase's
+// arithmetic and consumed after it) and handed to the cells' owners through shared memory.
 struct FusedPmlView {
     int n[3];                  // PML coordinates per axis (0: none)
     const int* map[3];         // coordinate → index into the axis' slab list, -1 outside the slabs
@@ -92,13 +93,22 @@ struct FusedPmlView {
     // separate buffer; the pointers are biased so that the index of plane nz (axis z: of slab entry n[2]) lands in it
     const float* gh_ghost[3][2];
     float* ge[3][2];           // ψ_E
+    // Dispatch order: the tile rows / plane chunks with slab work cost up to twice the others; launched last (high y, high z —
+    // where a slab sits) they are the tail of the grid.  heavy[a] = {p, s}: block indices [0, p) and [s, count) along y (a = 1)
+    // and z (a = 2) hold slab work and are mapped to the front: i → i (i < p), s + (i − p) (next count − s), else p + (i − p − (count − s)).
+    int heavy[3][2];
 };
+
+__device__ __forceinline__ int heavy_first(int i, int p, int s, int count) {
+    const int tail = count - s;
+    return i < p ? i : (i < p + tail ? s + (i - p) : i - tail);
+}
 
 template <int BY>
 struct FusedPmlSmem {
     static constexpr int XS = 32;     // x-slab cells of one tile row (both faces of a one-tile lattice: 2 × 16)
     static constexpr int ZMAX = 132;  // planes of one chunk + the recomputed plane above it
-    float xs[2][2][2][BY][XS];        // staged ψ of the x slabs: [iteration parity][half-step][G_ab | G_ac][row][entry]
+    float xg[2][2][BY][XS];           // ψ of the x slabs just advanced by lane j, for the cells' owners: [half-step][G_ab | G_ac][row][entry]
     float2 xbc[2][XS];                // (b, c) of each entry: [half-step]
     int xk[XS];                       // slab index of each entry
     int xl[XS];                       // tile column of each entry
@@ -108,14 +118,10 @@ struct FusedPmlSmem {
     float2 ybc[2][BY];
     int zk[ZMAX];
     float2 zbc[2][ZMAX];
+    int zwin[2];                      // first and last chunk-relative plane (0 … n) that lies in a z slab; first > last: none
 };
 
-__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all_but_last() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
 template <typename IdxT, int BX, int BY>
 struct FusedLayout {
@@ -173,8 +179,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const int tid = threadIdx.y * BX + threadIdx.x;
     const unsigned lane = tid & 31u;
     const int x0 = blockIdx.x * (4 * BX);
-    const int y0 = blockIdx.y * LO::CORE_ROWS;
-    const int za = V.z_lo + blockIdx.z * zc;
+    const int y0 = (PML ? heavy_first(blockIdx.y, Q.heavy[1][0], Q.heavy[1][1], gridDim.y) : static_cast<int>(blockIdx.y)) * LO::CORE_ROWS;
+    const int za = V.z_lo + (PML ? heavy_first(blockIdx.z, Q.heavy[2][0], Q.heavy[2][1], gridDim.z) : static_cast<int>(blockIdx.z)) * zc;
     const int zb = min(za + zc, V.z_hi);
     const int n = zb - za;
     const size_t sy = static_cast<size_t>(V.nx);
@@ -262,8 +268,13 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             S.zk[t] = kz;
             if (kz >= 0) { S.zbc[0][t] = __ldg(Q.bc_h[2] + kz); S.zbc[1][t] = __ldg(Q.bc_e[2] + kz); }
         }
+        if (tid == 0) { S.zwin[0] = PS::ZMAX; S.zwin[1] = -1; }
     }
     __syncthreads();
+    if (PML) {
+        for (int t = tid; t <= n && t < PS::ZMAX; t += NT)
+            if (S.zk[t] >= 0) { atomicMin(&S.zwin[0], t); atomicMax(&S.zwin[1], t); }
+    }
     // the recomputed column right of the tile (x0 + 128): its x-slab entry and (b, c), if a slab crosses the tile boundary there
     int xr_k = -1;
     float2 xr_bc = make_float2(0.f, 0.f);
@@ -271,8 +282,12 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         xr_k = __ldg(Q.map[0] + x0 + 4 * BX);
         if (xr_k >= 0) xr_bc = __ldg(Q.bc_h[0] + xr_k);
     }
-    int nxs = 0;          // x-slab cells of a tile row (entries of the staging rows)
+    int nxs = 0;          // x-slab cells of a tile row (entries of the hand-over rows)
     int xjp = -1;         // entries of the own quad's four cells, one signed byte each
+    // Most CTAs of a lattice touch no y or z slab at all: everything those slabs need per iteration (tests, prefetches, the
+    // blocks themselves) sits behind these CTA-uniform flags, so an interior CTA pays one branch per phase for them.
+    bool cta_y = false;   // one of the tile's rows lies in a y slab
+    int zw_lo = 1 << 30, zw_hi = -1;   // chunk-relative planes (0 … n) that lie in a z slab: inside [zw_lo, zw_hi]
     if (PML) {
         nxs = S.wcnt[0] + S.wcnt[1] + S.wcnt[2] + S.wcnt[3];
         if (tid < 4 * BX) {
@@ -284,6 +299,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         }
         __syncthreads();
         xjp = *reinterpret_cast<const int*>(&S.xj[4 * threadIdx.x]);
+#pragma unroll
+        for (int r = 0; r < BY; ++r) cta_y = cta_y || S.yk[r] >= 0;
+        zw_lo = S.zwin[0]; zw_hi = S.zwin[1];
     }
 
     const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
@@ -304,29 +322,13 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     float4 hxo = make_float4(0.f, 0.f, 0.f, 0.f), hyo = hxo, hzo = hxo;   // H'(z_k) of the own quad
     int mk_prev[4] = {0, 0, 0, 0};
 
-    // CPML: ψ of the row's x-slab cells for iteration kk → shared memory (4-byte cp.async copies, one entry per lane; each
-    // warp stages and reads its own row): ψ_H of plane z_kk for phase A, ψ_E of plane z_kk - 1 for phase B.  One commit
-    // group per call, also when nothing is copied, so that "all but the last group" is always "everything of this iteration".
-    auto stage_x = [&](int kk) {
-        if (PML) {
-            __syncwarp();
-            if (kk <= n && static_cast<int>(lane) < nxs && y < V.ny) {
-                const int kx = S.xk[lane];
-                if (kk < n_h) {
-                    const size_t qi = (static_cast<size_t>(za + kk) * V.ny + y) * Q.n[0] + kx;
-                    const bool ghost = za + kk == V.nz;
-                    cp_async4(&S.xs[kk & 1][0][0][ty][lane], (ghost ? Q.gh_ghost[0][0] : Q.gh_in[0][0]) + qi);
-                    cp_async4(&S.xs[kk & 1][0][1][ty][lane], (ghost ? Q.gh_ghost[0][1] : Q.gh_in[0][1]) + qi);
-                }
-                if (kk >= 1 && ty < LO::CORE_ROWS) {
-                    const size_t qi = (static_cast<size_t>(za + kk - 1) * V.ny + y) * Q.n[0] + kx;
-                    cp_async4(&S.xs[kk & 1][1][0][ty][lane], Q.ge[0][0] + qi);
-                    cp_async4(&S.xs[kk & 1][1][1][ty][lane], Q.ge[0][1] + qi);
-                }
-            }
-            cp_async_commit();
-        }
-    };
+    // CPML, x slabs: lane j owns the row's j-th x-slab cell for the whole march — its slab index and tile column never change
+    // (32-bit indices: the host keeps the recursion in the kernel only while an x-slab array has fewer than 2^31 entries)
+    const bool xlane = PML && static_cast<int>(lane) < nxs && y < V.ny;
+    int xl_j = 0;
+    unsigned xq_row = 0;  // index of (plane 0, row y, entry j) in the x-slab arrays [z][y][k]; a plane is ny·n[0] entries
+    if (xlane) { xl_j = S.xl[lane]; xq_row = static_cast<unsigned>(y) * static_cast<unsigned>(Q.n[0]) + static_cast<unsigned>(S.xk[lane]); }
+    const unsigned xq_plane = PML ? static_cast<unsigned>(V.ny) * static_cast<unsigned>(Q.n[0]) : 0u;
 
     for (int k = 0; k <= n; ++k) {
         const int zk = za + k;
@@ -334,31 +336,51 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         const float* e_cur = nullptr;
         float4 hxn = hxo, hyn = hyo, hzn = hzo;
         int mk_cur[4] = {0, 0, 0, 0};
-        if (PML && nxs) {
-            if (k == 0) stage_x(0);
-            stage_x(k + 1);          // one iteration ahead, like the TMA rings: its latency hides behind this iteration's work
-        }
-        if (PML && act) {
-            // the y- and z-slab ψ of the next iteration's quads (plain float4 loads there): pull the lines into L2 now
-            const int kk = k + 1, pky = S.yk[ty];
+        const bool zwin_a = PML && k >= zw_lo && k <= zw_hi;           // plane z_k (phase A) lies in a z slab — CTA-uniform
+        const bool zwin_b = PML && k - 1 >= zw_lo && k - 1 <= zw_hi;   // plane z_k - 1 (phase B) does
+        if (PML && (nxs || cta_y || (k + 1 >= zw_lo && k <= zw_hi)) && act) {
+            // the ψ of the next iteration's cells (plain loads there): pull the lines into L2 now
+            const int kk = k + 1;
             const bool nh = kk < n_h && za + kk < V.nz, ne = ty < LO::CORE_ROWS && kk <= n;
-            if (pky >= 0) {
-                const size_t q0 = (static_cast<size_t>(za + kk - 1) * Q.n[1] + pky) * sy + x, dq = static_cast<size_t>(Q.n[1]) * sy;
-                if (nh) { prefetch_l2(Q.gh_in[1][0] + q0 + dq); prefetch_l2(Q.gh_in[1][1] + q0 + dq); }
-                if (ne) { prefetch_l2(Q.ge[1][0] + q0); prefetch_l2(Q.ge[1][1] + q0); }
+            if (nxs) {
+                if (xlane) {
+                    const unsigned q0 = static_cast<unsigned>(za + kk) * xq_plane + xq_row;
+                    if (nh) { prefetch_l2(Q.gh_in[0][0] + q0); prefetch_l2(Q.gh_in[0][1] + q0); }
+                    if (ne) { prefetch_l2(Q.ge[0][0] + (q0 - xq_plane)); prefetch_l2(Q.ge[0][1] + (q0 - xq_plane)); }
+                }
             }
-            const int kzh = nh ? S.zk[kk] : -1, kze = ne ? S.zk[kk - 1] : -1;
-            if (kzh >= 0) {
-                const size_t q0 = (static_cast<size_t>(kzh) * V.ny + y) * sy + x;
-                prefetch_l2(Q.gh_in[2][0] + q0); prefetch_l2(Q.gh_in[2][1] + q0);
+            if (cta_y) {
+                const int pky = S.yk[ty];
+                if (pky >= 0) {
+                    const size_t q0 = (static_cast<size_t>(za + kk - 1) * Q.n[1] + pky) * sy + x, dq = static_cast<size_t>(Q.n[1]) * sy;
+                    if (nh) { prefetch_l2(Q.gh_in[1][0] + q0 + dq); prefetch_l2(Q.gh_in[1][1] + q0 + dq); }
+                    if (ne) { prefetch_l2(Q.ge[1][0] + q0); prefetch_l2(Q.ge[1][1] + q0); }
+                }
             }
-            if (kze >= 0) {
-                const size_t q0 = (static_cast<size_t>(kze) * V.ny + y) * sy + x;
-                prefetch_l2(Q.ge[2][0] + q0); prefetch_l2(Q.ge[2][1] + q0);
+            if (k + 1 >= zw_lo && k <= zw_hi) {
+                const int kzh = nh ? S.zk[kk] : -1, kze = ne ? S.zk[kk - 1] : -1;
+                if (kzh >= 0) {
+                    const size_t q0 = (static_cast<size_t>(kzh) * V.ny + y) * sy + x;
+                    prefetch_l2(Q.gh_in[2][0] + q0); prefetch_l2(Q.gh_in[2][1] + q0);
+                }
+                if (kze >= 0) {
+                    const size_t q0 = (static_cast<size_t>(kze) * V.ny + y) * sy + x;
+                    prefetch_l2(Q.ge[2][0] + q0); prefetch_l2(Q.ge[2][1] + q0);
+                }
             }
         }
         if (has_a) {
             const int e_idx = k + 1;
+            // CPML, x slabs: lane j's ψ_H of plane z_k — requested before the wait for the planes, used after the quad loop
+            float xp0 = 0.f, xp1 = 0.f;
+            if (PML && nxs) {
+                if (xlane) {
+                    const unsigned qi = static_cast<unsigned>(zk) * xq_plane + xq_row;
+                    const bool ghost = zk == V.nz;   // the plane above a z-slab: the upper neighbour's ψ_H, read-only here
+                    xp0 = __ldg((ghost ? Q.gh_ghost[0][0] : Q.gh_in[0][0]) + qi);
+                    xp1 = __ldg((ghost ? Q.gh_ghost[0][1] : Q.gh_in[0][1]) + qi);
+                }
+            }
             mbar_wait(fullE + (e_idx % LO::NE), static_cast<uint32_t>((e_idx / LO::NE) & 1));
             mbar_wait(fullH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
             if (k == 0 && below) mbar_wait(fullE + 0, 0u);
@@ -398,28 +420,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     s0 = lower_bound_ll(F.cells, F.n, cell);
                     while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
                 }
-                // CPML, x slabs: lane j advances ψ_H of the row's j-th x-slab cell (∂Ey/∂x, ∂Ez/∂x from the staged E plane) and
-                // leaves the new values in the staging row for the cell's owner; the row's owner stores them
                 const bool own_h = core && k < n;
-                if (PML && nxs) {
-                    cp_async_wait_all_but_last();
-                    if (static_cast<int>(lane) < nxs && gy < V.ny) {
-                        const int xl = S.xl[lane];
-                        const float* pj = e_cur + (r + 1) * PE + 4 + xl;
-                        const bool in = x0 + xl > 0;
-                        const float dey = in ? deriv<EXACT>(pj[E_COMP], pj[E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
-                        const float dez = in ? deriv<EXACT>(pj[2 * E_COMP], pj[2 * E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
-                        const float2 bc = S.xbc[0][lane];
-                        const float g0 = fmaf(bc.x, S.xs[k & 1][0][0][r][lane], bc.y * dey);
-                        const float g1 = fmaf(bc.x, S.xs[k & 1][0][1][r][lane], bc.y * dez);
-                        S.xs[k & 1][0][0][r][lane] = g0; S.xs[k & 1][0][1][r][lane] = g1;
-                        if (k < n && r < LO::CORE_ROWS) {
-                            const size_t qi = (static_cast<size_t>(zk) * V.ny + gy) * Q.n[0] + S.xk[lane];
-                            Q.gh_out[0][0][qi] = g0; Q.gh_out[0][1][qi] = g1;
-                        }
-                    }
-                    __syncwarp();
-                }
                 const float exv[4] = {ex.x, ex.y, ex.z, ex.w};
                 const float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
                 const float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
@@ -452,17 +453,42 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     hxv[q] = leap<EXACT>(c.z, hxv[q], c.w, -cx, mx);
                     hyv[q] = leap<EXACT>(c.z, hyv[q], c.w, -cy, my);
                     hzv[q] = leap<EXACT>(c.z, hzv[q], c.w, -cz, mz);
-                    if (PML && nxs) {   // x slabs: H_y += d_b·G_xz, H_z −= d_b·G_xy (k_pml_axis<0, 0>)
-                        const int j = ok ? (xjp << (24 - 8 * q)) >> 24 : -1;
-                        if (j >= 0) {
-                            hyv[q] = fmaf(c.w, S.xs[k & 1][0][1][r][j], hyv[q]);
-                            hzv[q] = fmaf(-c.w, S.xs[k & 1][0][0][r][j], hzv[q]);
-                        }
-                    }
                 }
                 };
                 if (!LEAN || has_src) h_quad(std::true_type{}); else h_quad(std::false_type{});
-                if (PML) {
+                if (PML && nxs) {
+                    // x slabs (k_pml_axis<0, 0>): lane j advances ψ_H of the row's j-th x-slab cell from ∂Ey/∂x, ∂Ez/∂x of the staged
+                    // E plane, stores it if this CTA owns the row, and hands it to the cell's owner, who adds H_y += d_b·G_xz,
+                    // H_z −= d_b·G_xy — outside the unrolled quad loop, so that the 28 lanes of a row without x-slab cells pay
+                    // one block of predicated instructions instead of four
+                    if (xlane) {
+                        const float* pj = e_cur + (r + 1) * PE + 4 + xl_j;
+                        const bool in = x0 + xl_j > 0;
+                        const float dey = in ? deriv<EXACT>(pj[E_COMP], pj[E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
+                        const float dez = in ? deriv<EXACT>(pj[2 * E_COMP], pj[2 * E_COMP - 1], V.dx[0], V.inv_dx[0]) : 0.f;
+                        const float2 bc = S.xbc[0][lane];
+                        const float g0 = fmaf(bc.x, xp0, bc.y * dey);
+                        const float g1 = fmaf(bc.x, xp1, bc.y * dez);
+                        S.xg[0][0][r][lane] = g0; S.xg[0][1][r][lane] = g1;
+                        if (k < n && r < LO::CORE_ROWS) {
+                            const unsigned qi = static_cast<unsigned>(zk) * xq_plane + xq_row;
+                            Q.gh_out[0][0][qi] = g0; Q.gh_out[0][1][qi] = g1;
+                        }
+                    }
+                    __syncwarp();
+                    if (xjp != -1 && ok) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const int j = (xjp << (24 - 8 * q)) >> 24;
+                            if (j >= 0) {
+                                const float w = coef(mk[q]).w;
+                                hyv[q] = fmaf(w, S.xg[0][1][r][j], hyv[q]);
+                                hzv[q] = fmaf(-w, S.xg[0][0][r][j], hzv[q]);
+                            }
+                        }
+                    }
+                }
+                if (PML && (cta_y || zwin_a)) {
                     // y and z slabs (whole rows / planes: warp- and CTA-uniform): G ← b·G + c·∂E/∂x_a from the staged planes
                     // again, H_b += d_b·G_ac, H_c −= d_b·G_ab; y before z as the passes run (k_pml_axis<0, 1>, <0, 2>)
                     const int pky = ok ? S.yk[r] : -1, pkz = ok ? S.zk[k] : -1;
@@ -584,6 +610,14 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         // ---- phase B: E'(z_k - 1) on the core tile ----------------------------------------------------------------
         if (k >= 1 && ty < LO::CORE_ROWS) {
             const int zp = zk - 1;
+            // CPML, x slabs: lane j's ψ_E of plane z_k - 1 — requested first, used after the quad loop
+            float xp0 = 0.f, xp1 = 0.f;
+            if (PML && nxs) {
+                if (xlane) {
+                    const unsigned qi = static_cast<unsigned>(zp) * xq_plane + xq_row;
+                    xp0 = Q.ge[0][0][qi]; xp1 = Q.ge[0][1][qi];
+                }
+            }
             const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (ty + 1) * PE + 4 + 4 * tx;
             const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + 4 * tx;
             float4 ex = ld4(e_own), ey = ld4(e_own + E_COMP), ez = ld4(e_own + 2 * E_COMP);
@@ -616,25 +650,6 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             float exv[4] = {ex.x, ex.y, ex.z, ex.w};
             float eyv[4] = {ey.x, ey.y, ey.z, ey.w};
             float ezv[4] = {ez.x, ez.y, ez.z, ez.w};
-            // CPML, x slabs: lane j advances ψ_E of the row's j-th x-slab cell (∂H'y/∂x, ∂H'z/∂x from the exchanged H' tile of
-            // plane z_k - 1) in place and leaves the new values in the staging row for the cell's owner
-            if (PML && nxs) {
-                cp_async_wait_all_but_last();
-                if (static_cast<int>(lane) < nxs && y < V.ny) {
-                    const int xl = S.xl[lane];
-                    const float* pj = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + xl;
-                    const bool in = x0 + xl + 1 < nx_cells;
-                    const float dhy = in ? deriv<EXACT>(pj[H_COMP + 1], pj[H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
-                    const float dhz = in ? deriv<EXACT>(pj[2 * H_COMP + 1], pj[2 * H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
-                    const float2 bc = S.xbc[1][lane];
-                    const float g0 = fmaf(bc.x, S.xs[k & 1][1][0][ty][lane], bc.y * dhy);
-                    const float g1 = fmaf(bc.x, S.xs[k & 1][1][1][ty][lane], bc.y * dhz);
-                    S.xs[k & 1][1][0][ty][lane] = g0; S.xs[k & 1][1][1][ty][lane] = g1;
-                    const size_t qi = (static_cast<size_t>(zp) * V.ny + y) * Q.n[0] + S.xk[lane];
-                    Q.ge[0][0][qi] = g0; Q.ge[0][1][qi] = g1;
-                }
-                __syncwarp();
-            }
             auto e_quad = [&](auto with_src) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -654,17 +669,38 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 exv[q] = leap<EXACT>(c.x, exv[q], c.y, cx, jx);
                 eyv[q] = leap<EXACT>(c.x, eyv[q], c.y, cy, jy);
                 ezv[q] = leap<EXACT>(c.x, ezv[q], c.y, cz, jz);
-                if (PML && nxs) {   // x slabs: E_y −= c_b·G_xz, E_z += c_b·G_xy (k_pml_axis<1, 0>)
-                    const int j = core ? (xjp << (24 - 8 * q)) >> 24 : -1;
-                    if (j >= 0) {
-                        eyv[q] = fmaf(-c.y, S.xs[k & 1][1][1][ty][j], eyv[q]);
-                        ezv[q] = fmaf(c.y, S.xs[k & 1][1][0][ty][j], ezv[q]);
-                    }
-                }
             }
             };
             if (!LEAN || has_src) e_quad(std::true_type{}); else e_quad(std::false_type{});
-            if (PML) {
+            if (PML && nxs) {
+                // x slabs (k_pml_axis<1, 0>): lane j advances ψ_E of the row's j-th x-slab cell in place from ∂H'y/∂x, ∂H'z/∂x of the
+                // exchanged H' tile of plane z_k - 1; the cell's owner adds E_y −= c_b·G_xz, E_z += c_b·G_xy
+                if (xlane) {
+                    const float* pj = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + xl_j;
+                    const bool in = x0 + xl_j + 1 < nx_cells;
+                    const float dhy = in ? deriv<EXACT>(pj[H_COMP + 1], pj[H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float dhz = in ? deriv<EXACT>(pj[2 * H_COMP + 1], pj[2 * H_COMP], V.dx[0], V.inv_dx[0]) : 0.f;
+                    const float2 bc = S.xbc[1][lane];
+                    const float g0 = fmaf(bc.x, xp0, bc.y * dhy);
+                    const float g1 = fmaf(bc.x, xp1, bc.y * dhz);
+                    S.xg[1][0][ty][lane] = g0; S.xg[1][1][ty][lane] = g1;
+                    const unsigned qi = static_cast<unsigned>(zp) * xq_plane + xq_row;
+                    Q.ge[0][0][qi] = g0; Q.ge[0][1][qi] = g1;
+                }
+                __syncwarp();
+                if (xjp != -1 && core) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int j = (xjp << (24 - 8 * q)) >> 24;
+                        if (j >= 0) {
+                            const float w = coef(mk_prev[q]).y;
+                            eyv[q] = fmaf(-w, S.xg[1][1][ty][j], eyv[q]);
+                            ezv[q] = fmaf(w, S.xg[1][0][ty][j], ezv[q]);
+                        }
+                    }
+                }
+            }
+            if (PML && (cta_y || zwin_b)) {
                 // y and z slabs: ψ_E advanced in place by the owner of E' (k_pml_axis<1, 1>, <1, 2>): E_b −= c_b·G_ac, E_c += c_b·G_ab
                 const int pky = core ? S.yk[ty] : -1, pkz = core ? S.zk[k - 1] : -1;
                 if (pky >= 0) {

@@ -69,12 +69,12 @@ def test_2d_kernel_fast_mode_and_true_division(b200, oracle, monkeypatch, size):
     assert np.array_equal(st2.read_field(b200.FieldComponent.H), ref2.field(oracle.H).astype(np.float32))
 
 
-def test_2d_kernel_u16_index_and_per_step_protocol(b200, oracle, monkeypatch):
+@pytest.mark.parametrize("n_mat", [300, 700])  # 700 rows: more than the kernel stages in shared memory (k2dTableMax = 512), read from global
+def test_2d_kernel_u16_index_and_per_step_protocol(b200, oracle, monkeypatch, n_mat):
     from fdtd_b200 import configs
 
     monkeypatch.delenv("FDTD_B200_TUNE", raising=False)
     rng = np.random.default_rng(3)
-    n_mat = 300
     pal = [b200.Material(1.0 + 0.001 * k, 0.0, 1.0 + 0.01 * k, 0.001 * (k % 5)) for k in range(n_mat)]
     size = (256, 20, 1)
     ids = rng.integers(0, n_mat, size[0] * size[1]).astype(np.uint32)
