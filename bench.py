@@ -457,14 +457,14 @@ def run_b200(args) -> None:
     st.set_source_table(pts, w.source_table(W))
     advance(W)
     barrier()
-    # one untimed probe pass sizes the number of passes: at least 5 (best of 5), more when K steps are short, so
-    # that the timed passes span >= ~0.6 s and the clock sampler sees them
+    # one untimed probe pass sizes the number of rounds: at least 5 (best of 5), more when K steps are short, so
+    # that the timed passes (three kinds per round, below) span >= ~0.6 s and the clock sampler sees them
     st.set_source_table(pts, w.source_table(K, t0=st.time()))
     st.timer_start()
     advance(K)
     probe_ms = max_over_ranks([st.timer_stop()])[0]
     barrier()
-    P = args.passes if args.passes > 0 else int(min(max(5, math.ceil(600.0 / max(probe_ms, 1e-3))), 60))
+    P = args.passes if args.passes > 0 else int(min(max(5, math.ceil(600.0 / max(3.3 * probe_ms, 1e-3))), 60))
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -526,13 +526,14 @@ def run_b200(args) -> None:
         barrier()
         return time.perf_counter() - c0
 
-    # The three kinds of pass alternate — device-resident, end to end, end to end with the lagging read — so that clock drift
-    # under the power cap (a B200 running this HBM-bound kernel reaches its cap after about a second) hits all of them alike,
-    # and each reports the median of its passes.  Three of the rounds add a pass with an event pair around every kernel launch:
+    # The three kinds of pass alternate in EVERY round — device-resident, end to end, end to end with the lagging read — so that
+    # clock drift under the power cap (a B200 running this HBM-bound kernel reaches its cap after 0.3 … 1 s, box by box) hits all
+    # of them alike, and each reports the median of its P passes.  (Until round 2 the end-to-end passes ran in the first 9 rounds
+    # only: on a box that throttled from round 12 on, `e2e` came out above `value`.)  Three of the rounds add a pass with an event pair around every kernel launch:
     # the dominant kernel's average duration for the roofline.  That instrumentation is kept out of the `value` passes: on
     # several GPUs the events sit between the boundary- and interior-stream launches of consecutive steps and cost 3 %
     # (N=2: 249 against 256 Gcells/s; N=1: 0.2 %).
-    EP = max(3, min(P, 9))
+    EP = P
     instrumented_rounds = {0, EP // 2, EP - 1}
     t0 = time.monotonic()
     pass_ms, e2e_passes, pipe_passes, prof_runs = [], [], [], []

@@ -35,7 +35,8 @@ def build_extension(force: bool = False, verbose: bool = False) -> str:
     """Compile the shared library if it is missing or older than its sources.  Returns its path."""
     if is_fresh() and not force:
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH, *_SOURCES, "-lcudart"]
+    # FDTD_B200_NVCC_EXTRA: extra flags for diagnostic builds (e.g. -DFDTD_B200_CTA_TRACE, tools/r02_cta_trace.sh); never set for the shipped library
+    cmd = [_nvcc(), *NVCC_FLAGS, *os.environ.get("FDTD_B200_NVCC_EXTRA", "").split(), "-o", LIB_PATH, *_SOURCES, "-lcudart"]
     env = dict(os.environ)
     # the image exports CXX/CC wrappers that lack OpenMP specs; nvcc only needs a plain host g++
     if os.path.exists("/usr/bin/g++"):

@@ -161,6 +161,10 @@ struct fdtd_b200_solver {
     // two slots by tick parity, each [axis x: G_ab, G_ac | axis y | axis z], plane sizes in ghost_plane[]
     float* psi_ghost = nullptr;
     size_t ghost_plane[3] = {0, 0, 0};
+#ifdef FDTD_B200_CTA_TRACE
+    unsigned long long* trace_buf = nullptr;
+    int trace_ctas = 0, trace_grid[4] = {0, 0, 0, 0};
+#endif
     bool has_pml = false;
     int heavy_key[3] = {-1, -1, -1};   // (z_lo, z_hi, zc) the cached dispatch order below was computed for; reset by pml_refresh_mode
     int heavy_val[2][2] = {{0, 0}, {0, 0}};   // FusedPmlView::heavy of the y and z block indices
@@ -539,11 +543,12 @@ int make_map(fdtd_b200_handle h, CUtensorMap* out, CUtensorMapDataType dt, size_
     return FDTD_B200_OK;
 }
 
-// Planes per CTA march of the fused kernel.  A march of zc planes costs zc + c plane-times (c ≈ 2.5: the extra old-E plane, the
-// ring fill and the recomputed H' plane above the chunk), the CTAs run in waves of 2 per SM, and the last wave leaves the GPU
-// partly idle for ≈ 0.43 of a march: cost(zc) = (ceil(tiles · chunks / slots) + 0.43) · (zc + c) with balanced chunks.
-// c and 0.43 are fitted to tools/exp_zc_midsize.sh (profiles/r01_exp_zc_midsize.txt: 256³ best at 16 planes, 384³ at 24,
-// 512³ at 32..64, 128 slower than the model says); the previous rule (halve 64 until 3 waves exist) left 384³ at 64 planes, 10 % slower.
+// Planes per CTA march of the fused kernel.  A march of zc planes costs zc + c plane-times (the extra old-E plane, the ring fill
+// and the recomputed H' plane above the chunk), the CTAs run in waves of 2 per SM, and the last wave leaves the GPU partly idle for
+// a fraction a of a march: cost(zc) = (ceil(tiles · chunks / slots) + a) · (zc + c) with balanced chunks.  Round 1 fitted a = 0.43,
+// c = 2.5 (profiles/r01_exp_zc_midsize.txt) — with the CTAs that hold a source or a probe running up to 29 % longer than the
+// others, which is what made a wave's end ragged.  With the per-plane source / probe masks in the kernel the same sweep over six
+// lattices fits a = 0.12, c = 2.0 and the model picks the measured best march in each (profiles/r02_exp_cta_trace.txt).
 int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunks = 1, int max_zc = 64) {
     if (h->n_sm == 0) {
         if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
@@ -558,7 +563,7 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunk
         const int chunks = (planes + zc - 1) / zc;
         if (chunks < min_chunks) continue;                // the peer-memory split wants a chunk per boundary plus an interior
         const int zce = (planes + chunks - 1) / chunks;   // balanced
-        const double cost = (std::ceil(static_cast<double>(tiles) * chunks / slots) + 0.43) * (zce + 2.5);
+        const double cost = (std::ceil(static_cast<double>(tiles) * chunks / slots) + 0.12) * (zce + 2.0);   // constants: profiles/r02_exp_cta_trace.txt
         if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = zce; }
     }
     return best;
@@ -623,9 +628,9 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
         // 4.76 with 64 (3.79 algorithmic); time: 1.446 / 1.399 / 1.397 / 1.413 / 1.517 ms (profiles/r02_exp_pml.txt).
         zc = pick_fused_zc(h, tiles, z_hi - z_lo, 1, pml ? 32 : 64);
     }
+    zc = std::min(zc, 128);       // the kernel's per-plane source / probe masks and FusedPmlSmem::ZMAX cover marches of at most 128 planes (+ the one above)
     FusedPmlView Q{};
     if (pml) {
-        zc = std::min(zc, 128);   // FusedPmlSmem::ZMAX planes of per-chunk coefficients
         for (int a = 0; a < 3; ++a) {
             const auto& A = h->pml[a];
             Q.n[a] = A.n; Q.map[a] = A.d_map; Q.bc_h[a] = A.d_bc[0]; Q.bc_e[a] = A.d_bc[1];
@@ -679,6 +684,17 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
             for (int c = 0; c < 2; ++c) V.push_up[c] = h->upper.field[pend][c];
     }
     if (raise_smem_limit(h, k, smem)) return fail(h, FDTD_B200_ECUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
+#ifdef FDTD_B200_CTA_TRACE
+    {   // diagnostic build: the last launch's per-CTA stamps go to the file FDTD_B200_CTA_TRACE_FILE names when the handle is destroyed
+        static unsigned long long* d_trace = nullptr;
+        if (!d_trace) {
+            CU_TRY(h, cudaMalloc(&d_trace, sizeof(unsigned long long) * 4 * 65536));
+            CU_TRY(h, cudaMemcpyToSymbol(g_cta_trace, &d_trace, sizeof(d_trace)));
+        }
+        h->trace_buf = d_trace; h->trace_ctas = static_cast<int>(std::min<size_t>(65536, static_cast<size_t>(grid.x) * grid.y * grid.z));
+        h->trace_grid[0] = grid.x; h->trace_grid[1] = grid.y; h->trace_grid[2] = grid.z; h->trace_grid[3] = zc;
+    }
+#endif
     k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc, Q);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
@@ -1526,6 +1542,22 @@ void fdtd_b200_destroy(fdtd_b200_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+#ifdef FDTD_B200_CTA_TRACE
+    if (const char* path = std::getenv("FDTD_B200_CTA_TRACE_FILE")) {
+        if (h->trace_buf && h->trace_ctas > 0) {
+            cudaDeviceSynchronize();
+            std::vector<unsigned long long> t(static_cast<size_t>(h->trace_ctas) * 4);
+            if (cudaMemcpy(t.data(), h->trace_buf, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
+                if (FILE* f = std::fopen(path, "w")) {
+                    std::fprintf(f, "# grid %d %d %d zc %d\n# cta smid start_ns end_ns x0 y0 za\n", h->trace_grid[0], h->trace_grid[1], h->trace_grid[2], h->trace_grid[3]);
+                    for (int i = 0; i < h->trace_ctas; ++i)
+                        std::fprintf(f, "%d %llu %llu %llu %llu %llu %llu\n", i, t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3] >> 40, (t[4 * i + 3] >> 20) & 0xfffff, t[4 * i + 3] & 0xfffff);
+                    std::fclose(f);
+                }
+            }
+        }
+    }
+#endif
     for (int c = 0; c < 6; ++c) if (h->alloc[c]) cudaFree(h->alloc[c]);
     for (int c = 0; c < 6; ++c) if (h->alt_alloc[c]) cudaFree(h->alt_alloc[c]);
     if (h->mat) cudaFree(h->mat);

@@ -129,6 +129,25 @@ __device__ __forceinline__ bool any_cell_in_box(const long long* __restrict__ ce
     return hit;
 }
 
+// The same scan, also recording WHICH planes of the box hold a cell: bit (z − z0) of `planes` (shared memory, zeroed by the
+// caller, ≥ (z1 − z0 + 31) / 32 words).  A marching kernel then pays for the per-cell lookups on those planes only.
+__device__ __forceinline__ bool mark_planes_in_box(const long long* __restrict__ cells, int n, int tid, int nthreads, int x0, int x1,
+                                                   int y0, int y1, int z0, int z1, int nx, long long sz, unsigned* planes) {
+    bool hit = false;
+    for (int s = tid; s < n; s += nthreads) {
+        const long long c = __ldg(cells + s);
+        const int z = static_cast<int>(c / sz);
+        const long long r = c - static_cast<long long>(z) * sz;
+        const int yy = static_cast<int>(r / nx);
+        const int xx = static_cast<int>(r - static_cast<long long>(yy) * nx);
+        if ((z >= z0) && (z < z1) && (yy >= y0) && (yy < y1) && (xx >= x0) && (xx < x1)) {
+            hit = true;
+            atomicOr(planes + ((z - z0) >> 5), 1u << ((z - z0) & 31));
+        }
+    }
+    return hit;
+}
+
 __device__ __forceinline__ float pick(const float4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
 
 // ------------------------------------------------------------------------------------------------

@@ -123,6 +123,13 @@ struct FusedPmlSmem {
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+#ifdef FDTD_B200_CTA_TRACE
+// Diagnostic build only (FDTD_B200_NVCC_EXTRA=-DFDTD_B200_CTA_TRACE): every CTA of a fused launch leaves (SM, start, end, tile) here
+__device__ unsigned long long* g_cta_trace = nullptr;
+__device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned smid() { unsigned s; asm volatile("mov.u32 %0, %%smid;" : "=r"(s)); return s; }
+#endif
+
 template <typename IdxT, int BX, int BY>
 struct FusedLayout {
     static constexpr int NT = BX * BY;
@@ -162,6 +169,10 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     uint64_t* fullH = fullE + LO::NE;                              // 2 barriers: … of an H ring slot
     uint64_t* emptyE = fullH + LO::NH;                             // 3 barriers: all BY warps have read the slot into registers
     uint64_t* emptyH = emptyE + LO::NE;                            // 2 barriers
+    // bytes 80 … 127 of the header: which planes of this CTA's march hold a source / a probe (bit k: plane za + k; a march is
+    // at most 128 planes + the recomputed one above: 5 words each)
+    unsigned* src_planes = reinterpret_cast<unsigned*>(smem_raw + 80);
+    unsigned* probe_planes = src_planes + 5;
     unsigned char* e_slots = smem_raw + 128;
     unsigned char* h_slots = e_slots + LO::NE * LO::E_SLOT_BYTES;
     float* hb = reinterpret_cast<float*>(h_slots + LO::NH * LO::H_SLOT_BYTES);   // 2 × 3 × H_COMP
@@ -190,6 +201,13 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const int last_h_plane = (zb < V.nz || V.hi_open != 0) ? zb : zb - 1;   // H'/old-E planes za..last_h_plane are needed
     const int n_h = last_h_plane - za + 1;                          // number of H-plane iterations with a phase A
 
+#ifdef FDTD_B200_CTA_TRACE
+    const size_t trace_at = 4 * (blockIdx.x + static_cast<size_t>(gridDim.x) * (blockIdx.y + static_cast<size_t>(gridDim.y) * blockIdx.z));
+    if (tid == 0 && g_cta_trace) {
+        g_cta_trace[trace_at] = smid(); g_cta_trace[trace_at + 1] = globaltimer_ns();
+        g_cta_trace[trace_at + 3] = (static_cast<unsigned long long>(x0) << 40) | (static_cast<unsigned long long>(y0) << 20) | static_cast<unsigned long long>(za);
+    }
+#endif
     const uint64_t ld_policy = l2_policy_evict_last();
     // ---- producer: one lane of the last warp issues 7 tensor copies per plane ------------------------------------
     auto issue_e = [&](int plane, int slot) {
@@ -231,6 +249,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     // 122.5, 1024×1024×128 127.7 vs 126.8, 4096×4096×1 68.0 vs 52.0; issuing after the first barrier instead is equal within
     // 0.3 %.  The PML instantiation measured 0.8 % slower with the early issue and keeps the late one.
     constexpr bool EARLY = !PML;
+    if (tid < 10) src_planes[tid] = 0u;   // (both masks; ordered before the scans by the __syncthreads below)
     if (tid == NT - 32) {
         for (int s = 0; s < LO::NE; ++s) mbar_init(fullE + s, 1);
         for (int s = 0; s < LO::NH; ++s) mbar_init(fullH + s, 1);
@@ -307,8 +326,11 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const long long sz_ll = static_cast<long long>(V.nx) * V.ny;
     // forcing may hit the recomputed halo as well: test the extended box
     bool has_src = false, has_probe = false;
-    if (F.n) has_src = __syncthreads_or(any_cell_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY, za, zb + 1, V.nx, sz_ll)) != 0;
-    if (P.n) has_probe = __syncthreads_or(any_cell_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + LO::CORE_ROWS, za, zb, V.nx, sz_ll)) != 0;
+    // … and which planes: a CTA that holds a source or a probe pays for the per-cell lookups on that plane only.  (Measured with
+    // per-CTA time stamps, 256³ in one wave of 64-plane marches: the source's CTA ran 165 µs and the probes' CTAs 137–144 µs against a
+    // median of 128 µs when every plane of their march did the lookups — and the slowest CTA of the wave is the kernel's time.)
+    if (F.n) has_src = __syncthreads_or(mark_planes_in_box(F.cells, F.n, tid, NT, x0, x0 + 4 * BX + 4, y0, y0 + BY, za, zb + 1, V.nx, sz_ll, src_planes)) != 0;
+    if (P.n) has_probe = __syncthreads_or(mark_planes_in_box(P.cells, P.n, tid, NT, x0, x0 + 4 * BX, y0, y0 + LO::CORE_ROWS, za, zb, V.nx, sz_ll, probe_planes)) != 0;
     if (!EARLY || V.late_issue) first_issue();
     if (n <= 0) return;
 
@@ -330,6 +352,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     if (xlane) { xl_j = S.xl[lane]; xq_row = static_cast<unsigned>(y) * static_cast<unsigned>(Q.n[0]) + static_cast<unsigned>(S.xk[lane]); }
     const unsigned xq_plane = PML ? static_cast<unsigned>(V.ny) * static_cast<unsigned>(Q.n[0]) : 0u;
 
+    // does chunk-relative plane i hold a source / a probe?  Read behind the loop-invariant has_src / has_probe only, so that the
+    // march of a CTA without any (all but a handful) stays the loop the compiler unswitches
+    auto plane_bit = [](const unsigned* mask, int i) -> bool { return (mask[i >> 5] >> (i & 31)) & 1u; };
     for (int k = 0; k <= n; ++k) {
         const int zk = za + k;
         const bool has_a = k < n_h;
@@ -415,7 +440,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 long long cell = 0;
                 int s0 = 0, cnt = 0;
                 if (!LEAN) cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
-                if (has_src) {
+                if (has_src && plane_bit(src_planes, k)) {
                     if (LEAN) cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
                     s0 = lower_bound_ll(F.cells, F.n, cell);
                     while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
@@ -455,7 +480,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     hzv[q] = leap<EXACT>(c.z, hzv[q], c.w, -cz, mz);
                 }
                 };
-                if (!LEAN || has_src) h_quad(std::true_type{}); else h_quad(std::false_type{});
+                if (!LEAN || has_src) h_quad(std::true_type{}); else h_quad(std::false_type{});   // (loop-invariant choice; on planes without a source cnt is 0)
                 if (PML && nxs) {
                     // x slabs (k_pml_axis<0, 0>): lane j advances ψ_H of the row's j-th x-slab cell from ∂Ey/∂x, ∂Ez/∂x of the staged
                     // E plane, stores it if this CTA owns the row, and hands it to the cell's owner, who adds H_y += d_b·G_xz,
@@ -568,7 +593,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                 const float cy = dex_dz - dez_dx;
                 const float cz = dey_dx - dex_dy;
                 float my = 0.f, mz = 0.f;
-                if (has_src) {
+                if (has_src && plane_bit(src_planes, k)) {
                     const long long cell = static_cast<long long>(zk) * sz_ll + static_cast<long long>(gy) * V.nx + gx;
                     const int s1 = lower_bound_ll(F.cells, F.n, cell);
                     if (s1 < F.n && __ldg(F.cells + s1) == cell) { my = __ldg(F.vals + 6 * s1 + 4); mz = __ldg(F.vals + 6 * s1 + 5); }
@@ -633,7 +658,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             long long cell = 0;
             int s0 = 0, cnt = 0;
             if (!LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
-            if (has_src) {
+            if (has_src && plane_bit(src_planes, k - 1)) {
                 if (LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
                 s0 = lower_bound_ll(F.cells, F.n, cell);
                 while (s0 + cnt < F.n && __ldg(F.cells + s0 + cnt) < cell + 4) ++cnt;
@@ -747,7 +772,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     if (zp == 0 && V.push_down[0] != nullptr) { st4(V.push_down[0] + pi, ex); st4(V.push_down[1] + pi, ey); st4(V.push_down[2] + pi, ez); }
                     if (zp == V.nz - 1 && V.push_up[0] != nullptr) { st4(V.push_up[0] + pi, ex); st4(V.push_up[1] + pi, ey); }
                 }
-                if (has_probe) {
+                if (has_probe && plane_bit(probe_planes, k - 1)) {
                     if (LEAN) cell = static_cast<long long>(zp) * sz_ll + static_cast<long long>(y) * V.nx + x;
                     for (int s = lower_bound_ll(P.cells, P.n, cell); s < P.n; ++s) {
                         const long long c = __ldg(P.cells + s);
@@ -779,6 +804,9 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
 
         __syncthreads();   // H'(z_k) tile complete before any warp reads it in the next iteration's phase B
     }
+#ifdef FDTD_B200_CTA_TRACE
+    if (tid == 0 && g_cta_trace) g_cta_trace[trace_at + 2] = globaltimer_ns();
+#endif
 }
 
 }  // namespace fdtd_b200
