@@ -66,8 +66,9 @@ struct fdtd_b200_solver {
     float* g[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool fused = false;
     std::string fused_why_not;      // why this handle is not on the fused step (empty when it is); fdtd_b200_step_path
-    FusedMaps fused_maps[2];        // TMA tensor maps of the two buffer sets (built at the first fused launch)
-    bool fused_maps_ready = false;
+    FusedMaps fused_maps[2][2];     // TMA tensor maps [tile width: 128 | 64 cells][buffer set] (built at the first fused launch of that width)
+    bool fused_maps_ready[2] = {false, false};
+    int narrow_tiles = -1;          // plain fused launches use the 64-cell tile (decided once per handle: use_narrow_tiles)
     int resident = -1;              // -1 not decided | 0 no | 1 one thread-block cluster | 2 cooperative grid (k_steps_resident)
     std::string resident_why_not;
     unsigned long long* d_sync = nullptr;      // grid-barrier slots of the resident kernel (one per CTA), epochs keep counting across launches
@@ -569,22 +570,39 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunk
     return best;
 }
 
-template <int EXACT, typename IdxT>
-int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) {
-    constexpr int BX = 32, BY = 8;
+// Tile width of the plain fused launches.  The 128-cell tile (one warp per thread row) wastes the lanes of a last tile column
+// that is mostly empty: 320 cells = 2.5 tiles run at 0.77 of the copy bandwidth, 448 = 3.5 at 0.87 (profiles/r02_exp_cta_trace.txt §3).
+// The 64-cell tile (two thread rows per warp, 15 core rows) covers such rows with whole tiles at the price of twice the x-halo
+// columns and right-column cells and of a producer warp that also owns a row of E' (forced onto 512³, where the wide tile fits
+// exactly: 119.0 against 129.7 Gcells/s); it is taken when it saves at least 10 % of the tile area — measured, wide → narrow:
+// 192³ 83.3 → 94.9, 320³ 105.7 → 116.7, 448³ 117.4 → 123.1, 300³ 101.2 → 103.5, 576³ 119.4 → 120.6 (profiles/r02_exp_narrow_tiles.txt).
+// FDTD_B200_NARROW_TILES=0 / 1 forces the choice.
+bool use_narrow_tiles(fdtd_b200_handle h) {
+    if (h->narrow_tiles < 0) {
+        const long long pad128 = (static_cast<long long>(h->nx) + 127) / 128 * 128, pad64 = (static_cast<long long>(h->nx) + 63) / 64 * 64;
+        bool narrow = pad64 < pad128 && static_cast<double>(pad128 - pad64) >= 0.10 * static_cast<double>(pad128);
+        if (const char* e = std::getenv("FDTD_B200_NARROW_TILES")) { if (e[0] == '0') narrow = false; if (e[0] == '1') narrow = true; }
+        h->narrow_tiles = narrow ? 1 : 0;
+    }
+    return h->narrow_tiles == 1;
+}
+
+template <int EXACT, typename IdxT, int BX, int BY>
+int launch_fused_w(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) {
     using LO = FusedLayout<IdxT, BX, BY>;
+    constexpr int W = BX == 32 ? 0 : 1;
     if (push && pml) return fail(h, FDTD_B200_ESTATE, "the peer-memory boundary launches do not carry a PML");
-    if (!h->fused_maps_ready) {
+    if (!h->fused_maps_ready[W]) {
         for (int set = 0; set < 2; ++set) {
             float* const* arr = (set == h->cur_set) ? h->alloc : h->alt_alloc;   // maps start at the lower ghost plane
             for (int c = 0; c < 3; ++c) {
-                if (int rc = make_map(h, &h->fused_maps[set].e[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[c], LO::PE, LO::E_ROWS, 2)) return rc;
-                if (int rc = make_map(h, &h->fused_maps[set].h[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[3 + c], LO::PE, LO::H_ROWS, 2)) return rc;
+                if (int rc = make_map(h, &h->fused_maps[W][set].e[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[c], LO::PE, LO::E_ROWS, 2)) return rc;
+                if (int rc = make_map(h, &h->fused_maps[W][set].h[c], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, arr[3 + c], LO::PE, LO::H_ROWS, 2)) return rc;
             }
-            if (int rc = make_map(h, &h->fused_maps[set].mat, sizeof(IdxT) == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
+            if (int rc = make_map(h, &h->fused_maps[W][set].mat, sizeof(IdxT) == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
                                   sizeof(IdxT), h->mat, LO::PM, LO::H_ROWS, 1)) return rc;   // + the upper neighbour's first plane
         }
-        h->fused_maps_ready = true;
+        h->fused_maps_ready[W] = true;
     }
     FusedView V{};
     for (int c = 0; c < 6; ++c) { V.in[c] = h->f[c]; V.out[c] = h->g[c]; }
@@ -673,9 +691,12 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
     }
     const size_t smem = LO::smem_bytes(V.table_in_smem ? V.n_table : 0, pml);
     const bool xpad = h->nxl != h->nx;
-    auto k = pml ? (xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, true, true> : k_step_fused<EXACT, IdxT, BX, BY, false, true, false>)
-                 : (push ? (xpad ? k_step_fused<EXACT, IdxT, BX, BY, true, false, true> : k_step_fused<EXACT, IdxT, BX, BY, true, false, false>)
-                         : (xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, false, true> : k_step_fused<EXACT, IdxT, BX, BY, false, false, false>));
+    auto k = xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, false, true> : k_step_fused<EXACT, IdxT, BX, BY, false, false, false>;
+    if constexpr (BX == 32) {   // the CPML and the peer-memory boundary instantiations exist for the 128-cell tile only
+        if (pml) k = xpad ? k_step_fused<EXACT, IdxT, BX, BY, false, true, true> : k_step_fused<EXACT, IdxT, BX, BY, false, true, false>;
+        else if (push) k = xpad ? k_step_fused<EXACT, IdxT, BX, BY, true, false, true> : k_step_fused<EXACT, IdxT, BX, BY, true, false, false>;
+    }
+    else if (pml || push) return fail(h, FDTD_B200_ESTATE, "internal: the 64-cell tile has no CPML / boundary instantiation");
     if (push) {   // boundary planes of the peer-memory transport: results also go into the neighbours' pending-set ghost planes
         const int pend = h->cur_set ^ 1;
         if (h->lower.present)
@@ -695,10 +716,16 @@ int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
         h->trace_grid[0] = grid.x; h->trace_grid[1] = grid.y; h->trace_grid[2] = grid.z; h->trace_grid[3] = zc;
     }
 #endif
-    k<<<grid, block, smem, h->stream>>>(h->fused_maps[h->cur_set], V, F, P, zc, Q);
+    k<<<grid, block, smem, h->stream>>>(h->fused_maps[W][h->cur_set], V, F, P, zc, Q);
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
+}
+
+template <int EXACT, typename IdxT>
+int launch_fused_t(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) {
+    if (!push && !pml && use_narrow_tiles(h)) return launch_fused_w<EXACT, IdxT, 16, 16>(h, z_lo, z_hi, push, pml);
+    return launch_fused_w<EXACT, IdxT, 32, 8>(h, z_lo, z_hi, push, pml);
 }
 
 // ---- CPML passes ---------------------------------------------------------------------------------
@@ -1832,6 +1859,7 @@ int fdtd_b200_step_path(fdtd_b200_handle h, char* buf, size_t cap) {
     } else if (h->fused) {
         s += "fused: k_step_fused<" + arith + "," + idx + ">";
         if (h->nx != h->nxl) s += " xpad";
+        if (!h->has_pml && use_narrow_tiles(h)) s += " 64-cell tiles (row pitch " + std::to_string(h->nx) + ": the last 128-cell tile column would be at most half full)";
         if (h->has_pml) s += h->pml_in_kernel ? " + CPML inside the kernel" : " + CPML passes (x slabs do not fit the in-kernel tiling, or FDTD_B200_PML_PASSES=1)";
         if (h->p2p) s += " + peer-memory halos";
     } else {

@@ -162,7 +162,12 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     constexpr int NT = LO::NT, PE = LO::PE, PM = LO::PM;
     constexpr int E_COMP = LO::E_COMP, H_COMP = LO::H_COMP;
     static_assert(LO::E_SLOT_BYTES % 128 == 0 && LO::H_SLOT_BYTES % 128 == 0 && LO::HB_BYTES % 128 == 0, "128-byte aligned slots");
-    static_assert(BX == 32 && BY <= 32, "one warp per thread row: the last warp issues the copies and owns the right-column cells");
+    // BX = 32, BY = 8: one warp per thread row, tile 128 cells × 7 core rows.  BX = 16, BY = 16 (plain instantiation only): two thread
+    // rows per warp, tile 64 cells × 15 core rows — for lattices whose last 128-cell tile column would be at most half full.  The last
+    // warp issues the copies and owns the right-column cells either way; with two rows per warp it also owns E' of row BY − 2.
+    static_assert((BX == 32 || BX == 16) && (BX * BY) % 32 == 0 && BY <= 32, "whole warps; the producer warp's lanes cover the BY right-column cells");
+    static_assert(BX == 32 || !PML, "the CPML blocks map lane j to the row's j-th x-slab cell: one thread row per warp");
+    constexpr int WARPS = BX * BY / 32;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers: TMA data of an E ring slot has landed
@@ -253,8 +258,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     if (tid == NT - 32) {
         for (int s = 0; s < LO::NE; ++s) mbar_init(fullE + s, 1);
         for (int s = 0; s < LO::NH; ++s) mbar_init(fullH + s, 1);
-        for (int s = 0; s < LO::NE; ++s) mbar_init(emptyE + s, BY);
-        for (int s = 0; s < LO::NH; ++s) mbar_init(emptyH + s, BY);
+        for (int s = 0; s < LO::NE; ++s) mbar_init(emptyE + s, WARPS);
+        for (int s = 0; s < LO::NH; ++s) mbar_init(emptyH + s, WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -338,6 +343,11 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     const int x = x0 + 4 * tx, y = y0 + ty;
     const bool act = (x < V.nx) && (y < V.ny);
     const bool core = act && (ty < LO::CORE_ROWS);                  // this thread owns E' of its quad
+    // phase B is entered warp by warp: a warp whose first thread row is a core row.  With one row per warp that is the thread's own
+    // `ty < CORE_ROWS`; with two, the last warp's upper half (row BY − 1) walks through phase B as a shadow of row BY − 2 — tyb keeps its
+    // shared-memory reads inside the tiles — and stores nothing (`core`).
+    const bool warp_core = ((tid & ~31) / BX) < LO::CORE_ROWS;
+    const int tyb = (BX == 32) ? ty : min(ty, LO::CORE_ROWS - 1);
     const int nx_cells = XPAD ? V.nxl : V.nx;                       // lattice cells of a row
     const int xlim = nx_cells - 1 - x;                              // XPAD: cell q of the quad has an x+1 neighbour iff q < xlim
 
@@ -633,7 +643,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         }
 
         // ---- phase B: E'(z_k - 1) on the core tile ----------------------------------------------------------------
-        if (k >= 1 && ty < LO::CORE_ROWS) {
+        if (k >= 1 && warp_core) {
             const int zp = zk - 1;
             // CPML, x slabs: lane j's ψ_E of plane z_k - 1 — requested first, used after the quad loop
             float xp0 = 0.f, xp1 = 0.f;
@@ -643,8 +653,8 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
                     xp0 = Q.ge[0][0][qi]; xp1 = Q.ge[0][1][qi];
                 }
             }
-            const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (ty + 1) * PE + 4 + 4 * tx;
-            const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + ty * PE + 4 + 4 * tx;
+            const float* e_own = reinterpret_cast<const float*>(e_slots + static_cast<size_t>(k % LO::NE) * LO::E_SLOT_BYTES) + (tyb + 1) * PE + 4 + 4 * tx;
+            const float* ph = hb + static_cast<size_t>((k - 1) & 1) * 3 * H_COMP + tyb * PE + 4 + 4 * tx;
             float4 ex = ld4(e_own), ey = ld4(e_own + E_COMP), ez = ld4(e_own + 2 * E_COMP);
             // last read of the old-E slot of plane z_k - 1 by this warp (phase A used it as the plane below)
             __syncwarp();
