@@ -659,6 +659,14 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
             // last read of the old-E slot of plane z_k - 1 by this warp (phase A used it as the plane below)
             __syncwarp();
             if (lane == 0) mbar_arrive(emptyE + (k % LO::NE));
+            if (BX != 32 && producer && k + 2 < n_h) {
+                // two thread rows per warp: the producer warp owns a row of E' too.  It re-arms the rings here — every warp releases
+                // these two slots at this point of its own phase B — instead of after its E' arithmetic, half an iteration later
+                if (lane == 0) mbar_wait(emptyH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
+                issue_h(zk + 2, k % LO::NH);
+                if (lane == 0) mbar_wait(emptyE + (k % LO::NE), static_cast<uint32_t>((k / LO::NE) & 1));
+                issue_e(zk + 2, k % LO::NE);
+            }
             const float4 hz = hzo;
             const float4 hz_yp = ld4(ph + 2 * H_COMP + PE), hx_yp = ld4(ph + PE);
             const float hz_r = ph[2 * H_COMP + 4], hy_r = ph[H_COMP + 4];
@@ -803,7 +811,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         // Refill as soon as the other warps have drained the slots — the top row's warp has no E' work and waits here in
         // their stead, so the copies of plane z_k + 2 start about half an iteration before the end-of-iteration barrier.
         // H ring slot k % 2 held z_k → z_k + 2;  E ring slot k % 3 held plane z_k - 1 → z_k + 2.
-        if (producer && k + 2 < n_h) {
+        if (producer && k + 2 < n_h && (BX == 32 || k == 0)) {   // (two rows per warp: done inside phase B, which iteration 0 does not have)
             if (lane == 0) mbar_wait(emptyH + (k % LO::NH), static_cast<uint32_t>((k / LO::NH) & 1));
             issue_h(zk + 2, k % LO::NH);
             if (lane == 0) mbar_wait(emptyE + (k % LO::NE), static_cast<uint32_t>((k / LO::NE) & 1));
