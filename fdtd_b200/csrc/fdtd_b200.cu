@@ -570,6 +570,21 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunk
     return best;
 }
 
+// Launch of a step kernel with programmatic stream serialization: if the previous operation of the stream is a kernel that
+// signals launch_dependents (the step kernels do, kernels.cuh), this launch's CTAs may become resident before that grid has
+// drained; they block in griddepcontrol.wait until it has.  FDTD_B200_NO_PDL=1 launches plainly (the A side of the A/B).
+template <typename... KArgs, typename... Args>
+cudaError_t launch_step_kernel(void (*k)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    static const bool pdl = [] { const char* e = std::getenv("FDTD_B200_NO_PDL"); return !(e && e[0] == '1'); }();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, k, std::forward<Args>(args)...);
+}
+
 // Tile width of the plain fused launches.  The 128-cell tile (one warp per thread row) wastes the lanes of a last tile column
 // that is mostly empty: 320 cells = 2.5 tiles run at 0.77 of the copy bandwidth, 448 = 3.5 at 0.87 (profiles/r02_exp_cta_trace.txt §3).
 // The 64-cell tile (two thread rows per warp, 15 core rows) covers such rows with whole tiles at the price of twice the x-halo
@@ -716,7 +731,7 @@ int launch_fused_w(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
         h->trace_grid[0] = grid.x; h->trace_grid[1] = grid.y; h->trace_grid[2] = grid.z; h->trace_grid[3] = zc;
     }
 #endif
-    k<<<grid, block, smem, h->stream>>>(h->fused_maps[W][h->cur_set], V, F, P, zc, Q);
+    CU_TRY(h, launch_step_kernel(k, grid, block, smem, h->stream, h->fused_maps[W][h->cur_set], V, F, P, zc, Q));
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
@@ -993,7 +1008,7 @@ int launch_2d_t(fdtd_b200_handle h) {
     if (const char* e = std::getenv("FDTD_B200_STEP2D_YC")) if (std::atoi(e) > 0) yc = std::atoi(e);
     const int items = n_xseg * ((V.ny + yc - 1) / yc);
     dim3 grid((items + k2dWarps - 1) / k2dWarps, 1, 1);
-    k<<<grid, 32 * k2dWarps, smem, h->stream>>>(V, forcing_view(h), probe_view(h), yc);
+    CU_TRY(h, launch_step_kernel(k, dim3(grid), dim3(32 * k2dWarps), smem, h->stream, V, forcing_view(h), probe_view(h), yc));
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;

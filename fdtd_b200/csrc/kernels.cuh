@@ -129,6 +129,13 @@ __device__ __forceinline__ bool any_cell_in_box(const long long* __restrict__ ce
     return hit;
 }
 
+// Programmatic dependent launch (griddepcontrol): a step kernel lets the next launch of the stream become resident as soon as all of
+// its own CTAs have started (launch_dependents at entry), and waits for the previous grid to complete and flush (wait) before its
+// first access to anything a step writes — fields, ψ, probe rows.  What runs before the wait (barrier set-up, coefficient table,
+// the per-CTA scans of the constant source / probe cell lists) overlaps the previous step's tail and the launch latency.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // The same scan, also recording WHICH planes of the box hold a cell: bit (z − z0) of `planes` (shared memory, zeroed by the
 // caller, ≥ (z1 − z0 + 31) / 32 words).  A marching kernel then pays for the per-cell lookups on those planes only.
 __device__ __forceinline__ bool mark_planes_in_box(const long long* __restrict__ cells, int n, int tid, int nthreads, int x0, int x1,

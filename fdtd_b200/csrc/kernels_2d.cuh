@@ -76,6 +76,7 @@ __device__ __forceinline__ void st4cs(float* p, const float4& v) { __stcs(reinte
 template <int EXACT, typename IdxT>
 __global__ void __launch_bounds__(32 * k2dWarps, 4)
 k_step_2d(const Step2dView V, const ForcingView F, const ProbeView P, const int yc) {
+    griddep_launch_dependents();
     extern __shared__ __align__(128) unsigned char smem_2d[];
     const unsigned lane = threadIdx.x & 31u;
     const int wic = threadIdx.x >> 5;
@@ -129,6 +130,7 @@ k_step_2d(const Step2dView V, const ForcingView F, const ProbeView P, const int 
         bulk_g2s(sl + 520, V.in[4] + g, row_bytes, bar);
         bulk_g2s(sl + 648, V.in[5] + g, row_bytes, bar);
     };
+    griddep_wait();   // the previous step's grid is complete (kernels.cuh): everything above overlapped its tail
     if (lane == 0) {
         for (int k = 0; k < k2dStages; ++k) mbar_init(full + k, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

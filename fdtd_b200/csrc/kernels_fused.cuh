@@ -169,6 +169,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
     static_assert(BX == 32 || !PML, "the CPML blocks map lane j to the row's j-th x-slab cell: one thread row per warp");
     constexpr int WARPS = BX * BY / 32;
 
+    griddep_launch_dependents();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* fullE = reinterpret_cast<uint64_t*>(smem_raw);       // 3 barriers: TMA data of an E ring slot has landed
     uint64_t* fullH = fullE + LO::NE;                              // 2 barriers: … of an H ring slot
@@ -263,6 +264,7 @@ k_step_fused(const __grid_constant__ FusedMaps M, const FusedView V, const Forci
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    griddep_wait();   // the previous step's grid is complete: its fields may be read, its inputs overwritten
     if (EARLY && !V.late_issue) first_issue();
     if (V.table_in_smem) {
         for (int t = tid; t < V.n_table; t += NT) s_tab[t] = V.table[t];
