@@ -555,12 +555,13 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunk
         if (cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->device) != cudaSuccess || h->n_sm <= 0) { (void)cudaGetLastError(); h->n_sm = 148; }
     }
     const double slots = 2.0 * h->n_sm;
-    static const int cand[] = {1, 2, 4, 6, 8, 12, 16, 20, 24, 28, 32, 40, 48, 56, 64};   // longer marches measured slower (128 planes: -6 %, profiles/r01_exp_plane_shape.txt)
+    // every march length up to the cap (longer marches measured slower: 128 planes −6 %, profiles/r01_exp_plane_shape.txt).  Round 1
+    // tried a coarse list (1, 2, 4, 6, 8, 12, 16, 20, …): on small lattices it misses the length that fills one wave — 128³ has 19
+    // tiles, 12 planes make 209 CTAs for 296 slots, 9 planes make 285.
     int best = std::max(1, std::min(planes, max_zc));
     double best_cost = 1e300;
-    for (int zc : cand) {
-        if (zc > max_zc) break;
-        if (zc > planes && zc != cand[0]) { if (best_cost < 1e300) break; }
+    for (int zc = 1; zc <= max_zc; ++zc) {
+        if (zc > planes && zc != 1) { if (best_cost < 1e300) break; }
         const int chunks = (planes + zc - 1) / zc;
         if (chunks < min_chunks) continue;                // the peer-memory split wants a chunk per boundary plus an interior
         const int zce = (planes + chunks - 1) / chunks;   // balanced

@@ -1,6 +1,6 @@
 #!/bin/bash
 # small 3-D lattices above the on-chip budget: which path, how fast
-for lat in 80,80,80 96,96,96 112,112,112 128,128,128 160,160,160 200,200,200; do
+for lat in ${LATS:-80,80,80 96,96,96 112,112,112 128,128,128 160,160,160 200,200,200}; do
   timeout 120 python bench.py --lattice $lat --steps 100 --warmup 10 --passes 9 --no-cpu-baseline --no-slab-parity 2>/dev/null | python -c "
 import json,sys
 try:
