@@ -1001,11 +1001,15 @@ int launch_2d_t(fdtd_b200_handle h) {
     // beats 3.1 waves) predicts 48 rows for 4096×4096 — and is wrong: 4096×4096×1 runs at 122.5 Gcells/s with 8-row marches, 115 with
     // 12–16, 108 with 32, 100 with 48, 113 with 4 (profiles/r02_exp_2d_kernel.txt), with a 3- or a 4-slot ring alike.  Warps that
     // march independently for long drift apart and their concurrent accesses lose DRAM-page / L2 locality; short marches re-align
-    // them every few rows, and the rows re-read at the seams (2 of 8) come from L2.  Lattices too small to fill the device's warp
-    // slots with 8-row items take 6- or 4-row marches.
+    // them every few rows, and the rows re-read at the seams (2 of 8) come from L2.  Smaller lattices are bound by the latency of
+    // a march, not by bandwidth, and want more, shorter ones: the longest of 8, 6, 4, 3 rows that still makes ≥ 1.6 waves of work
+    // items for the device's warp slots, else 2 rows.  Measured best (profiles/r02_exp_2d_kernel.txt): 600² 2 rows (10.0 µs per step
+    // against 11.7 with 4), 800² 2, 1000² 2 ≈ 4, 1400² 4 (19.8 against 21.5 with 6 and 23.9 with 8), 1700² 6, 2048² and above 8.
     const double warp_slots = static_cast<double>(h->step2d_slots) * k2dWarps;
-    int yc = std::min(V.ny, 8);
-    while (yc > 4 && static_cast<double>(n_xseg) * ((V.ny + yc - 1) / yc) < warp_slots) yc -= 2;
+    int yc = 2;
+    for (int c : {8, 6, 4, 3})
+        if (static_cast<double>(n_xseg) * ((V.ny + c - 1) / c) >= 1.6 * warp_slots) { yc = c; break; }
+    yc = std::max(1, std::min(yc, V.ny));
     if (const char* e = std::getenv("FDTD_B200_STEP2D_YC")) if (std::atoi(e) > 0) yc = std::atoi(e);
     const int items = n_xseg * ((V.ny + yc - 1) / yc);
     dim3 grid((items + k2dWarps - 1) / k2dWarps, 1, 1);
