@@ -502,12 +502,15 @@ std::string fused_refusal(uint32_t flags, int tune_variant, uint64_t pitch, int 
 }
 
 // Row pitch of a lattice of nx cells per row (see fdtd_b200_solver::nxl).  Rows of at least 64 cells are padded to the next
-// multiple of 16 (≤ 23 % more bytes), 97..127 cells to 128 (the fused kernel's tile); FDTD_B200_NO_ROW_PADDING=1 or the
-// generic-kernel flag keep the caller's nx, and so does a table that has no room for the pad row.
-uint64_t row_pitch(uint64_t nx, uint32_t flags, uint32_t n_table) {
-    if (nx % 16 == 0 || nx < 64 || (flags & FDTD_B200_FORCE_GENERIC_KERNELS) || n_table >= 65536) return nx;
+// multiple of 16 (≤ 23 % more bytes); rows of 96 … 127 cells to 128, one tile of the fused kernel (≤ 33 % more bytes — a multiple
+// of 16 among them too: 112³ ran the two-kernel path at 28.5 µs per step, profiles/r02_exp_narrow_tiles.txt);
+// FDTD_B200_NO_ROW_PADDING=1 or the generic-kernel flag keep the caller's nx, and so does a table that has no room for the pad row.
+// `cells`: cells of the handle (nx · ny · planes).  Rows of 96 or 112 cells need no padding to be stored, so a lattice of them that
+// fits the on-chip multi-step kernels (§3d of DESIGN.md: 148 SMs × 2048 cells) keeps its pitch — padding would push it over that budget.
+uint64_t row_pitch(uint64_t nx, uint32_t flags, uint32_t n_table, uint64_t cells) {
+    if (nx < 64 || (flags & FDTD_B200_FORCE_GENERIC_KERNELS) || n_table >= 65536) return nx;
     if (const char* e = std::getenv("FDTD_B200_NO_ROW_PADDING")) if (e[0] == '1') return nx;
-    if (nx > 96 && nx < 128) return 128;
+    if (nx >= 96 && nx < 128) return (nx % 16 == 0 && cells <= 303104) ? nx : 128;
     return (nx + 15) / 16 * 16;
 }
 
@@ -1338,7 +1341,10 @@ int create_common(const fdtd_b200_config* cfg, const fdtd_b200_coefficients_f32*
     auto* h = new fdtd_b200_solver();
     h->cfg = *cfg;
     h->nxl = cfg->nx; h->ny = cfg->ny; h->nz = cfg->nz;
-    h->nx = row_pitch(cfg->nx, cfg->flags, n_table);
+    {
+        const uint64_t ze = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
+        h->nx = row_pitch(cfg->nx, cfg->flags, n_table, static_cast<uint64_t>(cfg->nx) * cfg->ny * (ze - cfg->z_begin));
+    }
     h->n_table_user = n_table;
     if (h->nx != h->nxl) { h->pad_id = n_table; n_table += 1; }
     h->z_begin = cfg->z_begin;
@@ -1536,7 +1542,7 @@ size_t fdtd_b200_memory_required(const fdtd_b200_config* cfg, uint32_t index_byt
     if (!validate_cfg(cfg, &why) || (index_bytes != 1 && index_bytes != 2)) return 0;
     const uint64_t ze = (cfg->z_begin == 0 && cfg->z_end == 0) ? cfg->nz : cfg->z_end;
     const uint64_t nzl = ze - cfg->z_begin;
-    const uint64_t pitch = row_pitch(cfg->nx, cfg->flags, index_bytes == 1 ? 1 : 65535);
+    const uint64_t pitch = row_pitch(cfg->nx, cfg->flags, index_bytes == 1 ? 1 : 65535, static_cast<uint64_t>(cfg->nx) * cfg->ny * nzl);
     const uint64_t plane = pitch * cfg->ny;
     // 6 fp32 components with two ghost planes each + the material index (cf. 136 B/cell cpu/mod.rs:217-221,
     // 80 B/cell wgpu/mod.rs:129-133); the fused step keeps two sets of the fields

@@ -374,7 +374,8 @@ int fdtd_b200_write_field(fdtd_b200_handle h, int component, const uint64_t lo[3
 int fdtd_b200_device_field(fdtd_b200_handle h, int c, void** device_ptr);
 /* Cells per stored row.  The reference sizes its lattice as ceil(size/dx) (fdtd/mod.rs:24-29), so nx is rarely a multiple of
  * 16; the float4 / TMA kernels need 16-byte rows of every array, so lattices with nx >= 64 and nx % 16 != 0 are stored with
- * rows padded to the next multiple of 16 (97..127 → 128).  The pad cells index an internal all-zero coefficient row and stay
+ * rows padded to the next multiple of 16 (97..127 → 128, the fused kernel's tile; 96 and 112 too, once the lattice is larger than
+ * the on-chip kernels' 303 104-cell budget).  The pad cells index an internal all-zero coefficient row and stay
  * 0; they never influence a lattice cell (the x+1 boundary rule is applied at the caller's nx).  Everything that crosses this
  * ABI — linear cell indices of sources and probes, boxes, material ids, PML profiles, projections, the coefficient table —
  * is in terms of the caller's nx × ny × nz lattice; the pitch shows only in fdtd_b200_device_field, in the halo planes

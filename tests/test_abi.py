@@ -198,7 +198,7 @@ def test_product_package_never_imports_the_oracle():
 
 def test_memory_required_counts_the_row_pitch(b200, monkeypatch):
     """Lattices with nx >= 64 and nx % 16 != 0 are stored with padded rows (include/fdtd_b200.h, fdtd_b200_row_pitch):
-    150 -> 160, 100 -> 128 (the fused tile), 509 -> 512; below 64 cells, with the generic-kernel flag or with
+    150 -> 160, 96 … 127 -> 128 (the fused tile), 509 -> 512; below 64 cells, with the generic-kernel flag or with
     FDTD_B200_NO_ROW_PADDING=1 the caller's nx is kept.  Host-side rule, no GPU needed."""
     pc = b200.PhysicalConstants.REDUCED
     res = b200.Resolution((1.0, 1.0, 1.0), 0.25)
@@ -212,7 +212,12 @@ def test_memory_required_counts_the_row_pitch(b200, monkeypatch):
         return (12 if fused else 6) * 4 * plane * 10 + plane * 9 + 16
 
     assert need(150) == expect(160) and need(509) == expect(512) and need(100) == expect(128) and need(97) == expect(128)
-    assert need(96) == expect(96) and need(160) == expect(160) and need(63) == expect(63) and need(65) == expect(80)
+    assert need(95) == expect(96) and need(80) == expect(80)
+    # rows of 96 or 112 cells are padded to the fused tile only when the lattice is beyond the on-chip kernels' budget (303 104 cells)
+    assert need(96) == expect(96, fused=False) and need(112) == expect(112, fused=False)        # 96 x 10 x 8 cells: stays as it is
+    big = lambda nx: b200.FdtdB200Backend().memory_required(b200.FdtdSolverConfig.from_lattice((nx, 100, 80), res, pc))
+    assert big(96) == big(112) == big(128) == (12 * 4 * 128 * 100 * 82 + 128 * 100 * 81 + 16)
+    assert need(160) == expect(160) and need(63) == expect(63) and need(65) == expect(80)
     assert need(150) == expect(160, fused=True)                           # pitch >= 128: two buffer sets
     assert need(150, fused_step=False) == expect(160, fused=False)        # FDTD_B200_IN_PLACE_STEP
     assert need(70, fused_step=True) == expect(80, fused=False)           # pitch < 128: the fused kernel is not eligible
