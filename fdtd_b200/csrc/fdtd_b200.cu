@@ -577,9 +577,13 @@ int pick_fused_zc(fdtd_b200_handle h, long long tiles, int planes, int min_chunk
 // Launch of a step kernel with programmatic stream serialization: if the previous operation of the stream is a kernel that
 // signals launch_dependents (the step kernels do, kernels.cuh), this launch's CTAs may become resident before that grid has
 // drained; they block in griddepcontrol.wait until it has.  FDTD_B200_NO_PDL=1 launches plainly (the A side of the A/B).
+// `allow`: false for slabs with a neighbour — their step is a boundary launch (or two) on the priority stream and an interior launch
+// on the main stream, ordered by events; letting the second boundary launch overlap the first measured 2.3 % slower at N = 4
+// (493 against 505 Gcells/s, same box, profiles/r02_exp_pdl.txt).
 template <typename... KArgs, typename... Args>
-cudaError_t launch_step_kernel(void (*k)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
-    static const bool pdl = [] { const char* e = std::getenv("FDTD_B200_NO_PDL"); return !(e && e[0] == '1'); }();
+cudaError_t launch_step_kernel(void (*k)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool allow, Args&&... args) {
+    static const bool enabled = [] { const char* e = std::getenv("FDTD_B200_NO_PDL"); return !(e && e[0] == '1'); }();
+    const bool pdl = enabled && allow;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -735,7 +739,7 @@ int launch_fused_w(fdtd_b200_handle h, int z_lo, int z_hi, bool push, bool pml) 
         h->trace_grid[0] = grid.x; h->trace_grid[1] = grid.y; h->trace_grid[2] = grid.z; h->trace_grid[3] = zc;
     }
 #endif
-    CU_TRY(h, launch_step_kernel(k, grid, block, smem, h->stream, h->fused_maps[W][h->cur_set], V, F, P, zc, Q));
+    CU_TRY(h, launch_step_kernel(k, grid, block, smem, h->stream, !(h->lower.present || h->upper.present), h->fused_maps[W][h->cur_set], V, F, P, zc, Q));
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
@@ -1016,7 +1020,7 @@ int launch_2d_t(fdtd_b200_handle h) {
     if (const char* e = std::getenv("FDTD_B200_STEP2D_YC")) if (std::atoi(e) > 0) yc = std::atoi(e);
     const int items = n_xseg * ((V.ny + yc - 1) / yc);
     dim3 grid((items + k2dWarps - 1) / k2dWarps, 1, 1);
-    CU_TRY(h, launch_step_kernel(k, dim3(grid), dim3(32 * k2dWarps), smem, h->stream, V, forcing_view(h), probe_view(h), yc));
+    CU_TRY(h, launch_step_kernel(k, dim3(grid), dim3(32 * k2dWarps), smem, h->stream, true, V, forcing_view(h), probe_view(h), yc));
     h->launches += 1;
     CU_TRY(h, cudaGetLastError());
     return FDTD_B200_OK;
